@@ -1,0 +1,432 @@
+// HBM-bound row-wise kernels: LayerNorm fwd/bwd (+ fused gate backward), gate backward, column sums,
+// casts and the hi/lo split for the fp32-accurate GEMM mode.  One warp owns one row; 128-bit coalesced
+// accesses; reductions by warp shuffles; per-column partials live in registers across the rows a warp
+// visits and are flushed once per block with fp32 atomics.
+#include "gxa_host.h"
+
+namespace gxa {
+
+constexpr float kLnEps = 1e-5f;
+constexpr int RW_WARPS = 8;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ld4_bf16(const __nv_bfloat16* p) {
+  uint2 r = *reinterpret_cast<const uint2*>(p);
+  float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&r.x));
+  float2 b = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&r.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st4_bf16(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 r;
+  r.x = *reinterpret_cast<uint32_t*>(&a);
+  r.y = *reinterpret_cast<uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+__device__ __forceinline__ float4 ld4_any(const void* base, size_t idx, int is_f32) {
+  return is_f32 ? ld4(reinterpret_cast<const float*>(base) + idx)
+                : ld4_bf16(reinterpret_cast<const __nv_bfloat16*>(base) + idx);
+}
+__device__ __forceinline__ void st4_any(void* base, size_t idx, int is_f32, float4 v) {
+  if (is_f32) *reinterpret_cast<float4*>(reinterpret_cast<float*>(base) + idx) = v;
+  else st4_bf16(reinterpret_cast<__nv_bfloat16*>(base) + idx, v);
+}
+
+// ------------------------------------------------------------------ LayerNorm forward
+template <int NV>   // D = 128 * NV
+__global__ void __launch_bounds__(RW_WARPS * 32) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                               const float* __restrict__ b, void* __restrict__ out,
+                                                               int out_is_f32, float* __restrict__ mean,
+                                                               float* __restrict__ rstd, int rows) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * RW_WARPS + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float* xr = x + size_t(row) * D;
+  float4 v[NV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    v[i] = ld4(xr + i * 128 + lane * 4);
+    s += v[i].x + v[i].y + v[i].z + v[i].w;
+  }
+  const float mu = warp_sum(s) * (1.0f / D);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    float a = v[i].x - mu, bb = v[i].y - mu, c = v[i].z - mu, d = v[i].w - mu;
+    q += a * a + bb * bb + c * c + d * d;
+  }
+  const float rs = rsqrtf(warp_sum(q) * (1.0f / D) + kLnEps);
+  if (lane == 0) {
+    if (mean) mean[row] = mu;
+    if (rstd) rstd[row] = rs;
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = i * 128 + lane * 4;
+    float4 g = ld4(w + c), be = ld4(b + c), o;
+    o.x = (v[i].x - mu) * rs * g.x + be.x;
+    o.y = (v[i].y - mu) * rs * g.y + be.y;
+    o.z = (v[i].z - mu) * rs * g.z + be.z;
+    o.w = (v[i].w - mu) * rs * g.w + be.w;
+    st4_any(out, size_t(row) * D + c, out_is_f32, o);
+  }
+}
+
+#define GXA_NV_DISPATCH(D, CALL)                    \
+  switch ((D) / 128) {                              \
+    case 1: { constexpr int NV = 1; CALL; } break;  \
+    case 2: { constexpr int NV = 2; CALL; } break;  \
+    case 3: { constexpr int NV = 3; CALL; } break;  \
+    case 4: { constexpr int NV = 4; CALL; } break;  \
+    case 5: { constexpr int NV = 5; CALL; } break;  \
+    case 6: { constexpr int NV = 6; CALL; } break;  \
+    case 8: { constexpr int NV = 8; CALL; } break;  \
+    case 10: { constexpr int NV = 10; CALL; } break;\
+    default: return GXA_ERR_SHAPE;                  \
+  }
+
+static inline int check_launch() { count_launch(); return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA; }
+
+int ln_fwd(const float* x, const float* w, const float* b, void* out, int out_is_f32, float* mean, float* rstd, int rows,
+           int D, cudaStream_t s) {
+  if (D % 128) return GXA_ERR_SHAPE;
+  if (rows == 0) return 0;
+  const int grid = (rows + RW_WARPS - 1) / RW_WARPS;
+  GXA_NV_DISPATCH(D, (ln_fwd_kernel<NV><<<grid, RW_WARPS * 32, 0, s>>>(x, w, b, out, out_is_f32, mean, rstd, rows)));
+  return check_launch();
+}
+
+// ------------------------------------------------------------------ column-partial flush
+// Each warp holds, per lane, NV float4 partial column sums; combine the block's warps through
+// shared memory and issue one atomicAdd per column per block.
+template <int NV>
+__device__ __forceinline__ void flush_cols(float4 (&acc)[NV], float* __restrict__ dst, float* sm /*[RW_WARPS][128*NV]*/) {
+  constexpr int D = 128 * NV;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < NV; ++i) *reinterpret_cast<float4*>(sm + warp * D + i * 128 + lane * 4) = acc[i];
+  __syncthreads();
+  for (int c = threadIdx.x; c < D; c += RW_WARPS * 32) {
+    float t = 0.f;
+#pragma unroll
+    for (int wv = 0; wv < RW_WARPS; ++wv) t += sm[wv * D + c];
+    atomicAdd(dst + c, t);
+  }
+}
+
+// ------------------------------------------------------------------ LayerNorm backward (+ gate backward)
+template <int NV, bool GATED>
+__global__ void __launch_bounds__(RW_WARPS * 32)
+ln_bwd_kernel(const void* __restrict__ g, int g_is_f32, const float* __restrict__ x, const float* __restrict__ w,
+              const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ dres,
+              float* __restrict__ dx, float* __restrict__ dw, float* __restrict__ db, const void* __restrict__ o,
+              int o_is_f32, const float* __restrict__ gate, float* __restrict__ dgate_accum, void* __restrict__ dout,
+              float* __restrict__ dbias_out, int rows) {
+  constexpr int D = 128 * NV;
+  extern __shared__ float sm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float4 aw[NV], ab[NV], ao[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) aw[i] = ab[i] = ao[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float gate_t = 0.f, gacc = 0.f;
+  if (GATED) gate_t = tanhf(__ldg(gate));
+  float4 wv[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) wv[i] = ld4(w + i * 128 + lane * 4);
+
+  for (int row = blockIdx.x * RW_WARPS + warp; row < rows; row += gridDim.x * RW_WARPS) {
+    const size_t base = size_t(row) * D;
+    const float mu = mean[row], rs = rstd[row];
+    float4 gv[NV], xh[NV];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 128 + lane * 4;
+      gv[i] = ld4_any(g, base + c, g_is_f32);
+      float4 xv = ld4(x + base + c);
+      xh[i] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+      aw[i].x += gv[i].x * xh[i].x; aw[i].y += gv[i].y * xh[i].y; aw[i].z += gv[i].z * xh[i].z; aw[i].w += gv[i].w * xh[i].w;
+      ab[i].x += gv[i].x; ab[i].y += gv[i].y; ab[i].z += gv[i].z; ab[i].w += gv[i].w;
+      gv[i].x *= wv[i].x; gv[i].y *= wv[i].y; gv[i].z *= wv[i].z; gv[i].w *= wv[i].w;
+      s1 += gv[i].x + gv[i].y + gv[i].z + gv[i].w;
+      s2 += gv[i].x * xh[i].x + gv[i].y * xh[i].y + gv[i].z * xh[i].z + gv[i].w * xh[i].w;
+    }
+    s1 = warp_sum(s1) * (1.0f / D);
+    s2 = warp_sum(s2) * (1.0f / D);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 128 + lane * 4;
+      float4 r = dres ? ld4(dres + base + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 d;
+      d.x = r.x + rs * (gv[i].x - s1 - xh[i].x * s2);
+      d.y = r.y + rs * (gv[i].y - s1 - xh[i].y * s2);
+      d.z = r.z + rs * (gv[i].z - s1 - xh[i].z * s2);
+      d.w = r.w + rs * (gv[i].w - s1 - xh[i].w * s2);
+      *reinterpret_cast<float4*>(dx + base + c) = d;
+      if (GATED) {
+        float4 ov = ld4_any(o, base + c, o_is_f32);
+        gacc += d.x * ov.x + d.y * ov.y + d.z * ov.z + d.w * ov.w;
+        float4 t = make_float4(gate_t * d.x, gate_t * d.y, gate_t * d.z, gate_t * d.w);
+        if (!o_is_f32) {   // bf16 path: the bias gradient sums what the dgrad GEMM will see
+          t.x = __bfloat162float(__float2bfloat16_rn(t.x)); t.y = __bfloat162float(__float2bfloat16_rn(t.y));
+          t.z = __bfloat162float(__float2bfloat16_rn(t.z)); t.w = __bfloat162float(__float2bfloat16_rn(t.w));
+        }
+        st4_any(dout, base + c, o_is_f32, t);
+        ao[i].x += t.x; ao[i].y += t.y; ao[i].z += t.z; ao[i].w += t.w;
+      }
+    }
+  }
+  flush_cols<NV>(aw, dw, sm);
+  flush_cols<NV>(ab, db, sm);
+  if (GATED) {
+    flush_cols<NV>(ao, dbias_out, sm);
+    gacc = warp_sum(gacc);
+    if (lane == 0) atomicAdd(dgate_accum, gacc);
+  }
+}
+
+static inline int rowwise_grid(int rows) {
+  int blocks = (rows + RW_WARPS - 1) / RW_WARPS;
+  int cap = num_sms() * 4;
+  return blocks < cap ? blocks : cap;
+}
+
+int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const float* mean, const float* rstd,
+           const float* dres, float* dx, float* dw, float* db, const void* o, int o_is_f32, const float* gate,
+           float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s) {
+  if (D % 128) return GXA_ERR_SHAPE;
+  if (rows == 0) return 0;
+  const int grid = rowwise_grid(rows);
+  const size_t smem = sizeof(float) * RW_WARPS * D;
+  if (o != nullptr) {
+    GXA_NV_DISPATCH(D, (ln_bwd_kernel<NV, true><<<grid, RW_WARPS * 32, smem, s>>>(
+                           g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, o, o_is_f32, gate, dgate_accum, dout,
+                           dbias_out, rows)));
+  } else {
+    GXA_NV_DISPATCH(D, (ln_bwd_kernel<NV, false><<<grid, RW_WARPS * 32, smem, s>>>(
+                           g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, nullptr, 0, nullptr, nullptr, nullptr,
+                           nullptr, rows)));
+  }
+  return check_launch();
+}
+
+// ------------------------------------------------------------------ gate backward (FFN side)
+//   dout = tanh(gate) * dy      dgate_accum += sum(dy * f)      dbias += colsum(dout)
+template <int NV>
+__global__ void __launch_bounds__(RW_WARPS * 32)
+gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_is_f32, const float* __restrict__ gate,
+                float* __restrict__ dgate_accum, void* __restrict__ dout, int out_is_f32, float* __restrict__ dbias,
+                int rows) {
+  constexpr int D = 128 * NV;
+  extern __shared__ float sm[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float4 ao[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) ao[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float gate_t = tanhf(__ldg(gate));
+  float gacc = 0.f;
+  for (int row = blockIdx.x * RW_WARPS + warp; row < rows; row += gridDim.x * RW_WARPS) {
+    const size_t base = size_t(row) * D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = i * 128 + lane * 4;
+      float4 d = ld4(dy + base + c);
+      float4 fv = ld4_any(f, base + c, f_is_f32);
+      gacc += d.x * fv.x + d.y * fv.y + d.z * fv.z + d.w * fv.w;
+      float4 t = make_float4(gate_t * d.x, gate_t * d.y, gate_t * d.z, gate_t * d.w);
+      if (!out_is_f32) {
+        t.x = __bfloat162float(__float2bfloat16_rn(t.x)); t.y = __bfloat162float(__float2bfloat16_rn(t.y));
+        t.z = __bfloat162float(__float2bfloat16_rn(t.z)); t.w = __bfloat162float(__float2bfloat16_rn(t.w));
+      }
+      st4_any(dout, base + c, out_is_f32, t);
+      ao[i].x += t.x; ao[i].y += t.y; ao[i].z += t.z; ao[i].w += t.w;
+    }
+  }
+  flush_cols<NV>(ao, dbias, sm);
+  gacc = warp_sum(gacc);
+  if (lane == 0) atomicAdd(dgate_accum, gacc);
+}
+
+int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, float* dgate_accum, void* dout,
+             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s) {
+  if (D % 128) return GXA_ERR_SHAPE;
+  if (rows == 0) return 0;
+  const int grid = rowwise_grid(rows);
+  const size_t smem = sizeof(float) * RW_WARPS * D;
+  GXA_NV_DISPATCH(D, (gate_bwd_kernel<NV><<<grid, RW_WARPS * 32, smem, s>>>(dy, f, f_is_f32, gate, dgate_accum, dout,
+                                                                            out_is_f32, dbias, rows)));
+  return check_launch();
+}
+
+__global__ void gate_finish_kernel(const float* gate, const float* accum, float* dgate) {
+  const float t = tanhf(gate[0]);
+  dgate[0] += (1.0f - t * t) * accum[0];
+}
+int gate_finish(const float* gate, const float* accum, float* dgate, cudaStream_t s) {
+  gate_finish_kernel<<<1, 1, 0, s>>>(gate, accum, dgate);
+  return check_launch();
+}
+
+// ------------------------------------------------------------------ column sums: dst[c] += sum_r src[r, c]
+__global__ void __launch_bounds__(128) colsum_kernel(const void* __restrict__ src, int is_f32, int ld,
+                                                     float* __restrict__ dst, int rows, int cols, int rows_per_block) {
+  const int c = (blockIdx.x * 128 + threadIdx.x) * 2;
+  if (c >= cols) return;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float a0 = 0.f, a1 = 0.f;
+  if (is_f32) {
+    const float* p = reinterpret_cast<const float*>(src);
+    for (int r = r0; r < r1; ++r) {
+      float2 v = *reinterpret_cast<const float2*>(p + size_t(r) * ld + c);
+      a0 += v.x; a1 += v.y;
+    }
+  } else {
+    const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(src);
+    for (int r = r0; r < r1; ++r) {
+      float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p + size_t(r) * ld + c));
+      a0 += v.x; a1 += v.y;
+    }
+  }
+  atomicAdd(dst + c, a0);
+  atomicAdd(dst + c + 1, a1);
+}
+int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, cudaStream_t s) {
+  if (cols % 2) return GXA_ERR_SHAPE;
+  if (rows == 0) return 0;
+  const int gx = (cols / 2 + 127) / 128;
+  int gy = (num_sms() * 8 + gx - 1) / gx;
+  if (gy > (rows + 31) / 32) gy = (rows + 31) / 32;
+  if (gy < 1) gy = 1;
+  const int rpb = (rows + gy - 1) / gy;
+  colsum_kernel<<<dim3(gx, gy), 128, 0, s>>>(src, is_f32, ld, dst, rows, cols, rpb);
+  return check_launch();
+}
+
+// ------------------------------------------------------------------ casts / elementwise (n % 4 == 0)
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n4) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x)
+    st4_bf16(dst + 4 * i, ld4(src + 4 * i));
+}
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n4) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x)
+    *reinterpret_cast<float4*>(dst + 4 * i) = ld4_bf16(src + 4 * i);
+}
+static inline int ew_grid(size_t n4) {
+  size_t b = (n4 + 255) / 256;
+  size_t cap = size_t(num_sms()) * 8;
+  return int(b < cap ? (b ? b : 1) : cap);
+}
+int cast_f32_bf16(const float* src, void* dst, size_t n, cudaStream_t s) {
+  if (n % 4) return GXA_ERR_SHAPE;
+  if (n == 0) return 0;
+  cast_f32_bf16_kernel<<<ew_grid(n / 4), 256, 0, s>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n / 4);
+  return check_launch();
+}
+int cast_bf16_f32(const void* src, float* dst, size_t n, cudaStream_t s) {
+  if (n % 4) return GXA_ERR_SHAPE;
+  if (n == 0) return 0;
+  cast_bf16_f32_kernel<<<ew_grid(n / 4), 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(src), dst, n / 4);
+  return check_launch();
+}
+
+// hi = bf16(x), lo = bf16(x - hi):  x*y ~= hi_x*hi_y + lo_x*hi_y + hi_x*lo_y  (error ~2^-17 relative)
+__global__ void split3_kernel(const float* __restrict__ src, int ld, __nv_bfloat16* __restrict__ dst, int rows,
+                              int cols, int pattern, int along_rows) {
+  const size_t n4 = size_t(rows) * (cols / 4);
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+    const int r = int(i / (cols / 4)), c = int(i % (cols / 4)) * 4;
+    float4 v = ld4(src + size_t(r) * ld + c);
+    float4 hi = make_float4(__bfloat162float(__float2bfloat16_rn(v.x)), __bfloat162float(__float2bfloat16_rn(v.y)),
+                            __bfloat162float(__float2bfloat16_rn(v.z)), __bfloat162float(__float2bfloat16_rn(v.w)));
+    float4 lo = make_float4(v.x - hi.x, v.y - hi.y, v.z - hi.z, v.w - hi.w);
+    float4 seg1 = pattern == 0 ? lo : hi, seg2 = pattern == 0 ? hi : lo;
+    if (!along_rows) {
+      __nv_bfloat16* d = dst + size_t(r) * (3 * cols) + c;
+      st4_bf16(d, hi); st4_bf16(d + cols, seg1); st4_bf16(d + 2 * cols, seg2);
+    } else {
+      __nv_bfloat16* d = dst + size_t(r) * cols + c;
+      const size_t seg = size_t(rows) * cols;
+      st4_bf16(d, hi); st4_bf16(d + seg, seg1); st4_bf16(d + 2 * seg, seg2);
+    }
+  }
+}
+int split3(const float* src, int ld, void* dst, int rows, int cols, int pattern, int along_rows, cudaStream_t s) {
+  if (cols % 4) return GXA_ERR_SHAPE;
+  if (rows == 0) return 0;
+  split3_kernel<<<ew_grid(size_t(rows) * (cols / 4)), 256, 0, s>>>(src, ld, reinterpret_cast<__nv_bfloat16*>(dst), rows,
+                                                                   cols, pattern, along_rows);
+  return check_launch();
+}
+
+// kv_end[b] = 1 + index of the last key with mask == 0 (0 when every key is padded)
+__global__ void mask_kv_end_kernel(const uint8_t* __restrict__ mask, int* __restrict__ kv_end, int Lk) {
+  const int b = blockIdx.x;
+  int best = 0;
+  for (int j = threadIdx.x; j < Lk; j += 32)
+    if (mask[size_t(b) * Lk + j] == 0) best = j + 1;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (threadIdx.x == 0) kv_end[b] = best;
+}
+int mask_kv_end(const uint8_t* mask, int* kv_end, int B, int Lk, cudaStream_t s) {
+  if (B == 0) return 0;
+  mask_kv_end_kernel<<<B, 32, 0, s>>>(mask, kv_end, Lk);
+  return check_launch();
+}
+
+__global__ void gelu_f32_kernel(const float* __restrict__ u, float* __restrict__ a, size_t n) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    float v = u[i];
+    a[i] = 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
+  }
+}
+__global__ void gelu_bwd_f32_kernel(const float* __restrict__ da, const float* __restrict__ u, float* __restrict__ du,
+                                    size_t n) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    float v = u[i];
+    float cdf = 0.5f * (1.0f + erff(v * 0.70710678118654752f));
+    float pdf = 0.3989422804014327f * expf(-0.5f * v * v);
+    du[i] = da[i] * (cdf + v * pdf);
+  }
+}
+__global__ void gate_res_f32_kernel(const float* __restrict__ x, const float* __restrict__ o,
+                                    const float* __restrict__ gate, float* __restrict__ y, size_t n) {
+  const float t = tanhf(__ldg(gate));
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+    y[i] = x[i] + t * o[i];
+}
+__global__ void add_inplace_kernel(float* __restrict__ dst, const float* __restrict__ src, size_t n) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+    dst[i] += src[i];
+}
+int gelu_f32(const float* u, float* a, size_t n, cudaStream_t s) {
+  if (!n) return 0;
+  gelu_f32_kernel<<<ew_grid(n), 256, 0, s>>>(u, a, n);
+  return check_launch();
+}
+int gelu_bwd_f32(const float* da, const float* u, float* du, size_t n, cudaStream_t s) {
+  if (!n) return 0;
+  gelu_bwd_f32_kernel<<<ew_grid(n), 256, 0, s>>>(da, u, du, n);
+  return check_launch();
+}
+int gate_res_f32(const float* x, const float* o, const float* gate, float* y, size_t n, cudaStream_t s) {
+  if (!n) return 0;
+  gate_res_f32_kernel<<<ew_grid(n), 256, 0, s>>>(x, o, gate, y, n);
+  return check_launch();
+}
+int add_inplace_f32(float* dst, const float* src, size_t n, cudaStream_t s) {
+  if (!n) return 0;
+  add_inplace_kernel<<<ew_grid(n), 256, 0, s>>>(dst, src, n);
+  return check_launch();
+}
+
+}  // namespace gxa

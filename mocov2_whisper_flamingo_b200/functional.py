@@ -1,0 +1,280 @@
+"""autograd.Function wrappers over the C ABI (include/gxa.h).  PyTorch is plumbing here: it owns
+device memory, streams and the autograd graph; all arithmetic happens in libgxa_b200.so.
+
+Backward of every Function runs on the autograd engine thread; the entry points take the
+stream explicitly and keep no thread-local state.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import BlockPtrs, Dims, GXA_PREC_BF16, GXA_PREC_FP32, PARAM_FIELDS, check
+
+_default_precision: Optional[int] = None
+_workspaces: dict = {}
+
+
+def set_default_precision(p: Optional[str]) -> None:
+    """'bf16' | 'fp32' | None (None: bf16 under torch.autocast, else fp32 -- the reference's own rule)."""
+    global _default_precision
+    _default_precision = {None: None, "bf16": GXA_PREC_BF16, "fp32": GXA_PREC_FP32}[p]
+
+
+def resolve_precision(pref: Optional[int] = None) -> int:
+    if pref is not None:
+        return pref
+    if _default_precision is not None:
+        return _default_precision
+    return GXA_PREC_BF16 if torch.is_autocast_enabled("cuda") else GXA_PREC_FP32
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _require_cuda(t: torch.Tensor, what: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"gxa_b200: {what} must be a CUDA tensor (this path has no CPU fallback)")
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    return t.detach().to(torch.float32).contiguous()
+
+
+def workspace(nbytes: int, device: torch.device) -> torch.Tensor:
+    """Grow-only scratch buffer per (device, stream); kernels on one stream run in order so sharing is safe."""
+    key = (device.index, _stream())
+    w = _workspaces.get(key)
+    if w is None or w.numel() < nbytes:
+        w = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = w
+    return w
+
+
+# ---------------------------------------------------------------------------------------------
+# per-layer gradient bucket: the 14 gradients of a block as views of ONE flat fp32 buffer, so the
+# data-parallel all-reduce of a layer is a single collective.  Segments are padded to
+# 64 floats so every view is 256-byte aligned (vector atomics in the wgrad epilogues).
+# ---------------------------------------------------------------------------------------------
+def bucket_layout(D: int):
+    sizes = [1, 1, 3 * D * D, 3 * D, D * D, D, D, D, D, D, 4 * D * D, 4 * D, 4 * D * D, D]
+    offs, o = [], 0
+    for s in sizes:
+        offs.append(o)
+        o += (s + 63) // 64 * 64
+    return sizes, offs, o
+
+
+PARAM_SHAPES = lambda D: [(1,), (1,), (3 * D, D), (3 * D,), (D, D), (D,), (D,), (D,), (D,), (D,), (4 * D, D), (4 * D,),
+                          (D, 4 * D), (D,)]
+
+
+class BlockState:
+    """Per-module device state: the bf16 operand cache of the weights, refreshed when a weight changes."""
+
+    def __init__(self):
+        self.wcache = None
+        self.key = None
+
+    def refresh(self, dims: Dims, params, pp: BlockPtrs) -> torch.Tensor:
+        L = _lib.lib()
+        key = (dims.precision, dims.D) + tuple((p.data_ptr(), p._version) for p in params)
+        if self.wcache is None or self.key != key:
+            n = L.gxa_block_wcache_bytes(C.byref(dims))
+            if self.wcache is None or self.wcache.numel() != n:
+                self.wcache = torch.empty(n, dtype=torch.uint8, device=params[0].device)
+            check(L.gxa_block_prepare_weights(C.byref(dims), C.byref(pp), self.wcache.data_ptr(), _stream()),
+                  "gxa_block_prepare_weights")
+            self.key = key
+        return self.wcache
+
+
+class StackShared:
+    """State shared by the layers of one GatedCrossModalFusion call: xa is the same tensor for every
+    layer, so its operand form, the mask extents and the dxa accumulator exist once per stack."""
+
+    def __init__(self, xa: Optional[torch.Tensor], mask: Optional[torch.Tensor], precision: int, grad_hook=None):
+        self.precision = precision
+        self.mask_u8 = None
+        self.kv_end = None
+        self.xa_op = None
+        self.dxa = None
+        self.first_token = None      # identity of the first block call (its backward runs last)
+        self.grad_hook = grad_hook   # callable(layer_token, flat_bucket) -> None (data-parallel all-reduce)
+        L = _lib.lib()
+        if xa is not None:
+            if xa.dim() == 4 and xa.size(1) == 1:
+                xa = xa.squeeze(1)
+            if mask is not None and mask.dim() == 3 and mask.size(1) == 1:
+                mask = mask.squeeze(1)
+            B, Lk, D = xa.shape
+            if mask is not None:
+                if mask.dtype != torch.bool:
+                    raise AssertionError("only bool key_padding_mask is supported (True = padded key)")
+                assert mask.shape == (B, Lk), f"expecting key_padding_mask shape of {(B, Lk)}, but got {tuple(mask.shape)}"
+                self.mask_u8 = mask.contiguous().view(torch.uint8)
+                self.kv_end = torch.empty(B, dtype=torch.int32, device=xa.device)
+                check(L.gxa_mask_prepare(self.mask_u8.data_ptr(), self.kv_end.data_ptr(), B, Lk, _stream()),
+                      "gxa_mask_prepare")
+
+
+def _dims(B, Lq, Lk, D, H, precision, has_xa) -> Dims:
+    return Dims(B=B, Lq=Lq, Lk=max(Lk, 0), D=D, H=H, precision=precision, has_xa=int(has_xa), reserved=0)
+
+
+class BlockFn(torch.autograd.Function):
+    """GatedCrossAttentionBlock.forward / backward (reference: models/gate_cross_attention.py:28-50)."""
+
+    @staticmethod
+    def forward(ctx, x, xa, shared: StackShared, state: BlockState, n_heads: int, token, *params):
+        L = _lib.lib()
+        _require_cuda(x, "x")
+        B, Lq, D = x.shape
+        xf = _f32c(x)
+        has_xa = xa is not None
+        Lk = xa.shape[1] if has_xa else 0
+        dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa)
+        pd = [p.detach() for p in params]
+        for p in pd:
+            if p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("gxa_b200: block parameters must be contiguous fp32 (the reference's only "
+                                   "supported storage, SURVEY A.1 M8)")
+        pp = BlockPtrs(*[p.data_ptr() for p in pd])
+        wcache = state.refresh(dims, pd, pp)
+        if has_xa and shared.xa_op is None:
+            _require_cuda(xa, "xa")
+            n = L.gxa_xa_operand_bytes(C.byref(dims))
+            shared.xa_op = torch.empty(n, dtype=torch.uint8, device=x.device)
+            check(L.gxa_xa_prepare(C.byref(dims), _f32c(xa).data_ptr(), shared.xa_op.data_ptr(), _stream()),
+                  "gxa_xa_prepare")
+        if shared.first_token is None:
+            shared.first_token = token
+        nsaved = L.gxa_block_saved_bytes(C.byref(dims))
+        if nsaved == 0:
+            raise RuntimeError(f"gxa_b200: unsupported shape B={B} Lq={Lq} Lk={Lk} D={D} H={n_heads} "
+                               "(need head_dim 64 and d_model % 128 == 0)")
+        saved = torch.empty(nsaved, dtype=torch.uint8, device=x.device)
+        ws = workspace(L.gxa_block_workspace_bytes(C.byref(dims)), x.device)
+        y = torch.empty_like(xf)
+        check(L.gxa_block_fwd(C.byref(dims), C.byref(pp), wcache.data_ptr(), xf.data_ptr(), _p(shared.xa_op),
+                              _p(shared.mask_u8), _p(shared.kv_end), y.data_ptr(), saved.data_ptr(), ws.data_ptr(),
+                              _stream()), "gxa_block_fwd")
+        ctx.dims, ctx.shared, ctx.state, ctx.token = dims, shared, state, token
+        ctx.saved_buf, ctx.wcache = saved, wcache
+        ctx.xa_shape = tuple(xa.shape) if has_xa else None
+        ctx.x_dtype = x.dtype
+        ctx.save_for_backward(xf, *pd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.lib()
+        xf, *pd = ctx.saved_tensors
+        dims, shared = ctx.dims, ctx.shared
+        D = dims.D
+        dyf = _f32c(dy)
+        sizes, offs, total = bucket_layout(D)
+        bucket = torch.zeros(total, dtype=torch.float32, device=xf.device)
+        views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
+        pp = BlockPtrs(*[p.data_ptr() for p in pd])
+        gp = BlockPtrs(*[v.data_ptr() for v in views])
+        dx = torch.empty_like(xf)
+        dxa_ptr = None
+        if dims.has_xa:
+            if shared.dxa is None:
+                shared.dxa = torch.zeros(ctx.xa_shape, dtype=torch.float32, device=xf.device)
+            dxa_ptr = shared.dxa.data_ptr()
+        ws = workspace(L.gxa_block_workspace_bytes(C.byref(dims)), xf.device)
+        check(L.gxa_block_bwd(C.byref(dims), C.byref(pp), ctx.wcache.data_ptr(), xf.data_ptr(), _p(shared.xa_op),
+                              _p(shared.mask_u8), _p(shared.kv_end), ctx.saved_buf.data_ptr(), dyf.data_ptr(),
+                              dx.data_ptr(), dxa_ptr, C.byref(gp), ws.data_ptr(), _stream()), "gxa_block_bwd")
+        ctx.saved_buf = None
+        if shared.grad_hook is not None:
+            shared.grad_hook(ctx.token, bucket)
+        dxa = None
+        if dims.has_xa and ctx.token is shared.first_token:
+            dxa = shared.dxa          # every layer has accumulated into it by now
+            shared.dxa = None
+        grads = list(views)
+        if not dims.has_xa:           # attention parameters did not take part (reference: grad None)
+            for i in (0, 2, 3, 4, 5, 6, 7):
+                grads[i] = None
+        return (dx.to(ctx.x_dtype) if ctx.x_dtype != torch.float32 else dx, dxa, None, None, None, None, *grads)
+
+
+class LayerNormFn(torch.autograd.Function):
+    """LayerNorm.forward (reference: models/gate_cross_attention.py:8-10): fp32 statistics, output in x.dtype."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        L = _lib.lib()
+        _require_cuda(x, "x")
+        D = x.shape[-1]
+        xf = _f32c(x).view(-1, D)
+        rows = xf.shape[0]
+        out = torch.empty_like(xf)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty_like(mean)
+        w, b = _f32c(weight), _f32c(bias)
+        check(L.gxa_layernorm_fwd(xf.data_ptr(), w.data_ptr(), b.data_ptr(), out.data_ptr(), 1, mean.data_ptr(),
+                                  rstd.data_ptr(), rows, D, _stream()), "gxa_layernorm_fwd")
+        ctx.save_for_backward(xf, w, mean, rstd)
+        ctx.shape, ctx.dtype = x.shape, x.dtype
+        return out.view(x.shape).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        L = _lib.lib()
+        xf, w, mean, rstd = ctx.saved_tensors
+        rows, D = xf.shape
+        gf = _f32c(g).view(rows, D)
+        dx = torch.empty_like(xf)
+        dw = torch.zeros(D, dtype=torch.float32, device=xf.device)
+        db = torch.zeros_like(dw)
+        check(L.gxa_layernorm_bwd(gf.data_ptr(), xf.data_ptr(), w.data_ptr(), mean.data_ptr(), rstd.data_ptr(), None,
+                                  dx.data_ptr(), dw.data_ptr(), db.data_ptr(), rows, D, _stream()), "gxa_layernorm_bwd")
+        return dx.view(ctx.shape).to(ctx.dtype), dw, db
+
+
+class LinearFn(torch.autograd.Function):
+    """nn.Linear at the stack boundary (audio_proj / video_proj, gate_cross_attention.py:56-57, 64-65)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, precision: int):
+        L = _lib.lib()
+        _require_cuda(x, "x")
+        out_f, in_f = weight.shape
+        xf = _f32c(x).view(-1, in_f)
+        rows = xf.shape[0]
+        w, b = _f32c(weight), _f32c(bias)
+        y = torch.empty(rows, out_f, dtype=torch.float32, device=x.device)
+        ws = workspace(L.gxa_linear_workspace_bytes(rows, in_f, out_f, precision), x.device)
+        check(L.gxa_linear_fwd(xf.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), rows, in_f, out_f, precision,
+                               ws.data_ptr(), _stream()), "gxa_linear_fwd")
+        ctx.save_for_backward(xf, w)
+        ctx.precision, ctx.in_shape, ctx.x_dtype = precision, x.shape, x.dtype
+        ctx.need_dx = x.requires_grad
+        return y.view(*x.shape[:-1], out_f)
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.lib()
+        xf, w = ctx.saved_tensors
+        rows, in_f = xf.shape
+        out_f = w.shape[0]
+        dyf = _f32c(dy).view(rows, out_f)
+        dx = torch.empty_like(xf) if ctx.need_dx else None
+        dw = torch.zeros_like(w)
+        db = torch.zeros(out_f, dtype=torch.float32, device=xf.device)
+        ws = workspace(L.gxa_linear_workspace_bytes(rows, in_f, out_f, ctx.precision), xf.device)
+        check(L.gxa_linear_bwd(dyf.data_ptr(), xf.data_ptr(), w.data_ptr(), _p(dx), dw.data_ptr(), db.data_ptr(), rows,
+                               in_f, out_f, ctx.precision, ws.data_ptr(), _stream()), "gxa_linear_bwd")
+        return (dx.view(ctx.in_shape).to(ctx.x_dtype) if dx is not None else None), dw, db, None

@@ -1,0 +1,119 @@
+"""Drop-in replacements for the three classes of the reference's models/gate_cross_attention.py.
+
+Same class names, constructor arguments, ``forward`` signatures, padding-mask semantics
+(bool, True = padded key) and ``state_dict`` layout, so that
+
+    from mocov2_whisper_flamingo_b200.gate_cross_attention import GatedCrossModalFusion, LayerNorm
+
+can replace ``from .gate_cross_attention import ...`` in the reference's models/av_net.py:9 and a
+checkpoint written by the reference loads with ``strict=True``.  The torch sub-modules created here
+(``nn.MultiheadAttention``, ``nn.Sequential``) are *parameter containers only* -- they give the
+reference's exact parameter names, shapes, registration order and default initialisation; their
+``forward`` is never called.  All arithmetic runs in libgxa_b200.so (hand-written sm_100a CUDA).
+
+Precision: ``torch.autocast`` active (the reference's training mode, train.py:316) -> bf16 tensor-core
+contractions with fp32 LayerNorm/residual; otherwise fp32-accurate contractions (3xbf16 split) that
+match the reference's fp32 module to <= 1e-4.  Override with ``set_default_precision``.
+"""
+from __future__ import annotations
+
+import logging
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from .functional import (BlockFn, BlockState, LayerNormFn, LinearFn, StackShared, resolve_precision,
+                         set_default_precision)
+
+logger = logging.getLogger(__name__)
+
+__all__ = ["LayerNorm", "GatedCrossAttentionBlock", "GatedCrossModalFusion", "set_default_precision"]
+
+
+class LayerNorm(nn.LayerNorm):
+    """reference: models/gate_cross_attention.py:8-10 (fp32 statistics, result cast back to x.dtype)."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return LayerNormFn.apply(x, self.weight, self.bias)
+
+
+class GatedCrossAttentionBlock(nn.Module):
+    """reference: models/gate_cross_attention.py:12-50."""
+
+    def __init__(self, d_model, n_heads, dropout=0.1, enable_logging=False):
+        super().__init__()
+        self.enable_logging = enable_logging
+        # registration order mirrors the reference (:16-27) so state_dict() ordering is identical
+        self.attn = nn.MultiheadAttention(embed_dim=d_model, num_heads=n_heads, dropout=dropout, batch_first=True)
+        self.attn_ln = LayerNorm(d_model)
+        self.ff_ln = LayerNorm(d_model)
+        self.attn_gate = nn.Parameter(torch.tensor([0.]))
+        self.ff_gate = nn.Parameter(torch.tensor([0.]))
+        n_mlp = d_model * 4
+        self.ff = nn.Sequential(nn.Linear(d_model, n_mlp), nn.GELU(), nn.Linear(n_mlp, d_model), nn.Dropout(dropout))
+        self.d_model, self.n_heads, self.dropout = d_model, n_heads, dropout
+        self._state = BlockState()
+        self.precision: Optional[int] = None   # None: follow autocast / set_default_precision
+
+    def _params(self):
+        # order of _lib.PARAM_FIELDS
+        return (self.attn_gate, self.ff_gate, self.attn.in_proj_weight, self.attn.in_proj_bias,
+                self.attn.out_proj.weight, self.attn.out_proj.bias, self.attn_ln.weight, self.attn_ln.bias,
+                self.ff_ln.weight, self.ff_ln.bias, self.ff[0].weight, self.ff[0].bias, self.ff[2].weight,
+                self.ff[2].bias)
+
+    def forward(self, x, xa=None, mask=None, _shared: Optional[StackShared] = None):
+        if self.enable_logging:
+            logger.info(f"GatedCrossAttentionBlock input x shape: {x.shape}")
+            if xa is not None:
+                logger.info(f"Cross attention input xa shape: {xa.shape}")
+            if mask is not None:
+                logger.info(f"Attention mask shape: {mask.shape}")
+        if xa is not None and xa.dim() == 4 and xa.size(1) == 1:
+            xa = xa.squeeze(1)
+        if mask is not None and mask.dim() == 3 and mask.size(1) == 1:
+            mask = mask.squeeze(1)
+        if self.training and self.dropout > 0.0:
+            raise NotImplementedError("gxa_b200: dropout > 0 in training mode is not implemented yet "
+                                      "(construct with dropout=0.0 or call .eval())")
+        shared = _shared
+        if shared is None:
+            shared = StackShared(xa, mask if xa is not None else None, resolve_precision(self.precision))
+        y = BlockFn.apply(x, xa, shared, self._state, self.n_heads, self, *self._params())
+        if self.enable_logging:
+            logger.info(f"GatedCrossAttentionBlock output shape: {y.shape}")
+        return y
+
+
+class GatedCrossModalFusion(nn.Module):
+    """reference: models/gate_cross_attention.py:52-73 (audio_mask is accepted and ignored there too)."""
+
+    def __init__(self, d_model, n_heads, n_layers, dropout=0.1, enable_logging=False):
+        super().__init__()
+        self.enable_logging = enable_logging
+        self.audio_proj = nn.Linear(d_model, d_model)
+        self.video_proj = nn.Linear(d_model, d_model)
+        self.layers = nn.ModuleList([GatedCrossAttentionBlock(d_model, n_heads, dropout,
+                                                              enable_logging=self.enable_logging)
+                                     for _ in range(n_layers)])
+        self.ln_post = LayerNorm(d_model)
+        self.precision: Optional[int] = None
+        self.grad_hook = None    # set by parallel.DataParallelGrads: per-layer gradient all-reduce
+
+    def forward(self, audio_features, video_features, audio_mask=None, video_mask=None):
+        if self.enable_logging:
+            logger.info(f"Fusion input audio_features shape: {audio_features.shape}")
+            logger.info(f"Fusion input video_features shape: {video_features.shape}")
+        prec = resolve_precision(self.precision)
+        x = LinearFn.apply(audio_features, self.audio_proj.weight, self.audio_proj.bias, prec)
+        xa = LinearFn.apply(video_features, self.video_proj.weight, self.video_proj.bias, prec)
+        if self.enable_logging:
+            logger.info(f"After projection, x shape: {x.shape}, xa shape: {xa.shape}")
+        shared = StackShared(xa, video_mask, prec, grad_hook=self.grad_hook)
+        for layer in self.layers:
+            x = layer(x, xa, video_mask, _shared=shared)
+        x = LayerNormFn.apply(x, self.ln_post.weight, self.ln_post.bias)
+        if self.enable_logging:
+            logger.info(f"Fusion output shape: {x.shape}")
+        return x

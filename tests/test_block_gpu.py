@@ -1,0 +1,125 @@
+"""Parity of the CUDA path (through the drop-in modules, hence through the C ABI) with
+ (a) golden outputs of the live reference module (tests/golden, made by oracle/make_golden.py) and
+ (b) the float64 oracle on the same seeded inputs.
+Tolerances (BASELINE.json north_star): fp32 mode 1e-4 relative, bf16 mode 2e-2 relative, rel = max|a-b|/max|b|;
+mask semantics exact."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from oracle import gxa_oracle as O
+import mocov2_whisper_flamingo_b200 as G
+from gpu_util import np_dev, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = {"fp32": 1e-4, "bf16": 2e-2}
+
+
+def load(name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    B, Lq, Lk, D, H, nl, seed = (int(v) for v in g["spec"])
+    kind = "fusion" if name.startswith("fusion") else ("noxa" if "noxa" in name else "block")
+    shapes = O.fusion_param_shapes(D, nl) if kind == "fusion" else O.block_param_shapes(D)
+    p = O.make_params(shapes, seed, *[float(v) for v in g["gates"]])
+    x, xa, mask, dy = O.make_inputs(B, Lq, max(Lk, 1), D, seed, list(g["lengths"]))
+    return g, kind, (B, Lq, Lk, D, H, nl), p, x, xa, mask, dy
+
+
+def build(kind, D, H, nl, p):
+    mod = G.GatedCrossModalFusion(D, H, nl, dropout=0.0) if kind == "fusion" else G.GatedCrossAttentionBlock(D, H, dropout=0.0)
+    mod.load_state_dict({k: torch.from_numpy(v) for k, v in p.items()}, strict=True)
+    return mod.cuda()
+
+
+def run(mod, kind, x, xa, mask, dy, prec):
+    G.set_default_precision(prec)
+    try:
+        xt = np_dev(x).requires_grad_(True)
+        xat = np_dev(xa).requires_grad_(True)
+        mt = torch.from_numpy(mask).cuda()
+        mod.zero_grad(set_to_none=True)
+        if kind == "fusion":
+            y = mod(xt, xat, video_mask=mt)
+        elif kind == "noxa":
+            y = mod(xt)
+        else:
+            y = mod(xt, xat, mt)
+        y.backward(np_dev(dy))
+        torch.cuda.synchronize()
+        grads = {k: v.grad for k, v in mod.named_parameters()}
+        return y.detach(), xt.grad, (xat.grad if kind != "noxa" else None), grads
+    finally:
+        G.set_default_precision(None)
+
+
+def compare_grad(name, mine, ref, tol):
+    ref = torch.as_tensor(np.asarray(ref)).double()
+    mine = mine.double().cpu()
+    if name.endswith("in_proj_bias"):
+        # the bk third is mathematically zero (softmax shift invariance): absolute tolerance
+        D = ref.shape[0] // 3
+        assert mine[D:2 * D].abs().max() <= tol * max(1.0, float(mine.abs().max())), name
+        idx = torch.cat([torch.arange(0, D), torch.arange(2 * D, 3 * D)])
+        mine, ref = mine[idx], ref[idx]
+    den = float(ref.abs().max())
+    if den == 0:
+        assert float(mine.abs().max()) <= 1e-6, name
+    else:
+        assert float((mine - ref).abs().max()) / den < tol, f"{name}: {float((mine - ref).abs().max()) / den:.3e}"
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", ["block_small", "block_masked", "block_gate0", "block_noxa", "fusion_small", "block_c1"])
+def test_parity_with_reference_and_oracle(name, prec):
+    g, kind, (B, Lq, Lk, D, H, nl), p, x, xa, mask, dy = load(name)
+    mod = build(kind, D, H, nl, p)
+    y, dx, dxa, grads = run(mod, kind, x, xa, mask, dy, prec)
+    tol = TOL[prec]
+    assert torch.isfinite(y).all()
+    assert rel_err(y.cpu(), torch.from_numpy(g["y"])) < tol                   # (a) live-reference golden
+    if kind == "fusion":
+        yo, c = O.fusion_forward(p, x, xa, mask, H, nl)
+        go, dxo, dxao = O.fusion_backward(p, c, dy)
+    else:
+        yo, c = O.block_forward(p, x, None if kind == "noxa" else xa, None if kind == "noxa" else mask, H)
+        go, dxo, dxao = O.block_backward(p, c, dy)
+    assert rel_err(y.cpu(), torch.from_numpy(yo)) < tol                       # (b) float64 oracle
+    gtol = tol if prec == "fp32" else 3e-2   # bf16: gradients pass through two more bf16 roundings than y
+    assert rel_err(dx.cpu(), torch.from_numpy(dxo)) < gtol
+    if dxa is not None:
+        assert rel_err(dxa.cpu(), torch.from_numpy(dxao)) < gtol
+        m = torch.from_numpy(mask)
+        assert (dxa.cpu()[m] == 0).all()                                      # padded keys: exactly zero gradient
+    for k, ref in go.items():
+        if ref is None:
+            assert grads[k] is None or float(grads[k].abs().max()) == 0.0, k
+        else:
+            compare_grad(k, grads[k], ref, gtol)
+
+
+def test_gate0_is_identity_bit_exact():
+    g, kind, (B, Lq, Lk, D, H, nl), p, x, xa, mask, dy = load("block_gate0")
+    mod = build(kind, D, H, nl, p)
+    for prec in ("fp32", "bf16"):
+        y, *_ = run(mod, kind, x, xa, mask, dy, prec)
+        assert torch.equal(y.cpu(), torch.from_numpy(x))
+
+
+def test_masked_keys_bit_exact_no_influence():
+    g, kind, (B, Lq, Lk, D, H, nl), p, x, xa, mask, dy = load("block_masked")
+    mod = build(kind, D, H, nl, p)
+    xa_clean = np.where(mask[:, :, None], 0.0, xa).astype(np.float32)
+    for prec in ("fp32", "bf16"):
+        y1, dx1, _, _ = run(mod, kind, x, xa, mask, dy, prec)
+        y2, dx2, _, _ = run(mod, kind, x, xa_clean, mask, dy, prec)
+        assert torch.equal(y1, y2) and torch.equal(dx1, dx2)
+
+
+def test_state_dict_layout_matches_reference_order():
+    blk = G.GatedCrossAttentionBlock(128, 2, dropout=0.0)
+    assert list(blk.state_dict().keys()) == list(O.BLOCK_KEYS)
+    fus = G.GatedCrossModalFusion(128, 2, 3, dropout=0.0)
+    assert list(fus.state_dict().keys()) == list(O.fusion_param_shapes(128, 3).keys())

@@ -1,0 +1,94 @@
+"""tcgen05 GEMM (gxa_gemm_bf16) vs torch fp32 matmul of the same bf16 operands.
+bf16 x bf16 products are exact in fp32, so only the summation order differs: tolerance 2e-5 relative."""
+import math
+
+import pytest
+import torch
+
+from mocov2_whisper_flamingo_b200 import _lib
+from gpu_util import err_map, gemm, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-5
+
+
+def operands(M, N, K, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    A = torch.randn(M, K, device="cuda", generator=g).to(torch.bfloat16)
+    B = torch.randn(N, K, device="cuda", generator=g).to(torch.bfloat16)
+    return A, B
+
+
+def ref_mm(A, B):
+    return A.float() @ B.float().t()
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K,bn", [(128, 128, 64, 128), (128, 256, 128, 256), (500, 384, 384, 0),
+                                      (1000, 1536, 200, 0), (896, 512, 1024, 256), (3000, 1024, 520, 0)])
+def test_layouts_f32(a_mn, b_mn, M, N, K, bn):
+    if (a_mn and M % 8) or (b_mn and N % 8) or ((not a_mn or not b_mn) and K % 8):
+        # TMA needs 16-byte row pitch: the contiguous dimension of each operand must be a multiple of 8
+        if (a_mn and M % 8) or (not a_mn and K % 8) or (b_mn and N % 8) or (not b_mn and K % 8):
+            pytest.skip("row pitch not 16-byte aligned for this layout")
+    A, B = operands(M, N, K)
+    Cm, _ = gemm(A, B, a_mn, b_mn, bn=bn)
+    R = ref_mm(A, B)
+    e = rel_err(Cm, R)
+    assert e < TOL, f"rel err {e:.3e}\n{err_map(Cm, R)}"
+
+
+@pytest.mark.parametrize("ks", [2, 3, 4])
+def test_split_k_and_accumulate(ks):
+    A, B = operands(256, 256, 1000, seed=1)
+    R = ref_mm(A, B)
+    Cm, _ = gemm(A, B, True, True, k_splits=ks)
+    assert rel_err(Cm, R) < TOL
+    C0 = torch.randn(256, 256, device="cuda")
+    Cm, _ = gemm(A, B, False, True, accumulate=1, C_init=C0, k_splits=1)
+    assert rel_err(Cm, R + C0) < TOL
+
+
+def test_auto_split_wgrad_shape():
+    # wgrad-like: few output tiles, long contraction (tokens) -> auto split-K
+    A, B = operands(384, 384, 5000, seed=2)
+    Cm, _ = gemm(A, B, True, True)
+    assert rel_err(Cm, ref_mm(A, B)) < TOL
+
+
+def test_epilogue_bias_bf16():
+    A, B = operands(300, 768, 384, seed=3)
+    bias = torch.randn(768, device="cuda")
+    Cm, _ = gemm(A, B, epi=_lib.EPI_BF16, bias=bias)
+    R = (ref_mm(A, B) + bias).to(torch.bfloat16)
+    assert rel_err(Cm.float(), R.float()) < 8e-3        # one bf16 ulp
+    assert (Cm.float() - R.float()).abs().max() <= 2 * 2 ** -8 * R.float().abs().max()
+
+
+def test_epilogue_gate_residual():
+    A, B = operands(300, 384, 384, seed=4)
+    bias = torch.randn(384, device="cuda")
+    X = torch.randn(300, 384, device="cuda")
+    gate = torch.tensor([0.7], device="cuda")
+    Y, O = gemm(A, B, epi=_lib.EPI_GATE_RES, bias=bias, aux=X, gate=gate)
+    o_ref = (ref_mm(A, B) + bias).to(torch.bfloat16)
+    assert rel_err(O.float(), o_ref.float()) < 8e-3
+    y_ref = X + math.tanh(0.7) * O.float()               # exact given the stored O
+    assert rel_err(Y, y_ref) < 1e-6
+
+
+def test_epilogue_bias_gelu_and_backward():
+    A, B = operands(260, 1536, 384, seed=5)
+    bias = torch.randn(1536, device="cuda")
+    U, Act = gemm(A, B, epi=_lib.EPI_BIAS_GELU, bias=bias)
+    u_ref = (ref_mm(A, B) + bias).to(torch.bfloat16)
+    assert rel_err(U.float(), u_ref.float()) < 8e-3
+    a_ref = torch.nn.functional.gelu(U.float()).to(torch.bfloat16)
+    assert rel_err(Act.float(), a_ref.float()) < 8e-3
+    # GELU backward epilogue: dU = bf16(dA) * gelu'(U), with dA = dF @ W2 (B operand MN-major as in dgrad)
+    dF, W2t = operands(260, 1536, 384, seed=6)           # dF [260,384], W2^T logical [1536,384]
+    dU, _ = gemm(dF, W2t, False, True, epi=_lib.EPI_GELU_BWD, aux=U)
+    dA = ref_mm(dF, W2t).to(torch.bfloat16).float()
+    u = U.float().requires_grad_(True)
+    torch.nn.functional.gelu(u).backward(dA)
+    assert rel_err(dU.float(), u.grad) < 1e-2

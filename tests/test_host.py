@@ -1,0 +1,82 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/gxa.h declares, the host
+shell mirrors the reference's module interface (names, ctor args, state_dict layout, error types) and
+refuses to run without CUDA (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, ROOT
+from oracle import gxa_oracle as O
+import mocov2_whisper_flamingo_b200 as G
+from mocov2_whisper_flamingo_b200 import _lib
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "gxa.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gxa_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    assert os.path.exists(_lib.LIB_PATH), "build with python -m mocov2_whisper_flamingo_b200.build"
+    L = C.CDLL(_lib.LIB_PATH)
+    syms = header_symbols()
+    assert len(syms) >= 20
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/gxa.h but not exported"
+    assert set(syms) == set(_lib.SIGNATURES), "ctypes signatures out of sync with include/gxa.h"
+    assert b"sm_100a" in _lib.lib().gxa_version()
+
+
+def test_size_queries_are_host_only_and_consistent():
+    L = _lib.lib()
+    d = _lib.Dims(B=2, Lq=448, Lk=250, D=384, H=6, precision=0, has_xa=1, reserved=0)
+    assert L.gxa_block_wcache_bytes(C.byref(d)) == 12 * 384 * 384 * 2
+    sv, ws = L.gxa_block_saved_bytes(C.byref(d)), L.gxa_block_workspace_bytes(C.byref(d))
+    assert sv > 2 * 448 * 384 * (4 + 2 * 5 + 2 * 8) and ws > 0
+    bad = _lib.Dims(B=2, Lq=448, Lk=250, D=384, H=5, precision=0, has_xa=1, reserved=0)   # head_dim != 64
+    assert L.gxa_block_saved_bytes(C.byref(bad)) == 0
+    assert L.gxa_block_fwd(C.byref(bad), None, None, None, None, None, None, None, None, None, None) == -1
+
+
+def test_state_dict_layout_and_strict_load():
+    blk = G.GatedCrossAttentionBlock(128, 2, dropout=0.0)
+    assert list(blk.state_dict().keys()) == list(O.BLOCK_KEYS)
+    assert {k: tuple(v.shape) for k, v in blk.state_dict().items()} == O.block_param_shapes(128)
+    fus = G.GatedCrossModalFusion(128, 2, 3)
+    shapes = O.fusion_param_shapes(128, 3)
+    assert list(fus.state_dict().keys()) == list(shapes.keys())
+    p = O.make_params(shapes, 3)
+    fus.load_state_dict({k: torch.from_numpy(v) for k, v in p.items()}, strict=True)
+    assert fus.layers[1].attn_gate.item() == pytest.approx(0.7)        # gates stay readable Parameters (monitor.py)
+    assert fus.layers[1].ff_gate.item() == pytest.approx(-0.4)
+
+
+def test_init_matches_reference_defaults():
+    blk = G.GatedCrossAttentionBlock(128, 2)
+    assert blk.attn_gate.item() == 0.0 and blk.ff_gate.item() == 0.0     # identity at init (A.1 M6)
+    assert float(blk.attn.in_proj_bias.abs().max()) == 0.0 and float(blk.attn.out_proj.bias.abs().max()) == 0.0
+    assert tuple(blk.ff[0].weight.shape) == (512, 128)                   # hidden = 4 * d_model
+
+
+def test_error_conventions():
+    with pytest.raises(AssertionError, match="embed_dim must be divisible by num_heads"):
+        G.GatedCrossAttentionBlock(100, 3)
+    blk = G.GatedCrossAttentionBlock(128, 2, dropout=0.0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        blk(torch.randn(1, 4, 128), torch.randn(1, 4, 128))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        G.LayerNorm(128)(torch.randn(2, 128))
+    with pytest.raises(NotImplementedError):
+        G.GatedCrossAttentionBlock(128, 2, dropout=0.1).train()(torch.randn(1, 4, 128))
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "mocov2_whisper_flamingo_b200")
+    for f in os.listdir(pkg):
+        if f.endswith(".py"):
+            assert "oracle" not in open(os.path.join(pkg, f)).read(), f
