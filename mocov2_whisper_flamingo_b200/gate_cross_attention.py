@@ -101,6 +101,12 @@ class GatedCrossModalFusion(nn.Module):
         self.precision: Optional[int] = None
         self.grad_hook = None    # set by parallel.DataParallelGrads: per-layer gradient all-reduce
 
+    def invalidate_weight_cache(self):
+        """Force the bf16 operand cache of every layer to be rebuilt on the next forward (the cache is
+        otherwise refreshed automatically when a weight's version counter changes, e.g. after optimizer.step())."""
+        for layer in self.layers:
+            layer._state.key = None
+
     def forward(self, audio_features, video_features, audio_mask=None, video_mask=None):
         if self.enable_logging:
             logger.info(f"Fusion input audio_features shape: {audio_features.shape}")

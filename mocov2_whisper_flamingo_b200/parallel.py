@@ -1,0 +1,84 @@
+"""Batch-sharded data parallelism for the fusion stack: one process per GPU, full replica, and ONE
+collective on the path -- the gradient all-reduce (reference: train.py:319 DDPStrategy).
+
+Each layer's 14 gradients live in one flat fp32 bucket (functional.bucket_layout).  As soon as a layer's
+backward call has been enqueued, its bucket is all-reduced with NCCL on a dedicated communication
+stream (ordered after the layer's kernels by an event), so the NVLink/NVSwitch traffic of layer i
+overlaps the backward kernels of layers i-1 .. 0.  ``finish()`` makes the compute stream wait for the
+communication stream and reduces the few stack-level parameters (audio_proj, video_proj, ln_post).
+
+Use ``zero_grad(set_to_none=True)`` (torch's default): autograd then adopts the bucket views as
+``.grad`` without copying, and the in-place all-reduce lands directly in ``.grad``.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+class DataParallelGrads:
+    def __init__(self, fusion, process_group: Optional[dist.ProcessGroup] = None, average: bool = True):
+        self.fusion = fusion
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.average = average
+        self.comm_stream = torch.cuda.Stream() if torch.cuda.is_available() else None
+        self.pending: List = []
+        self.buckets: List[torch.Tensor] = []
+        fusion.grad_hook = self._on_layer_grads
+
+    # called from BlockFn.backward (autograd thread) right after the layer's kernels were enqueued
+    def _on_layer_grads(self, token, bucket: torch.Tensor) -> None:
+        if self.world == 1:
+            return
+        if self.comm_stream is None:           # CPU/gloo (tests): synchronous
+            if self.average:
+                bucket.div_(self.world)
+            dist.all_reduce(bucket, group=self.pg)
+            return
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream())
+        with torch.cuda.stream(self.comm_stream):
+            self.comm_stream.wait_event(ready)
+            if self.average:
+                bucket.div_(self.world)
+            self.pending.append(dist.all_reduce(bucket, group=self.pg, async_op=True))
+        bucket.record_stream(self.comm_stream)
+        self.buckets.append(bucket)
+
+    def broadcast_parameters(self, src: int = 0) -> None:
+        if self.world == 1:
+            return
+        for p in self.fusion.parameters():
+            dist.broadcast(p.data, src, group=self.pg)
+
+    def finish(self) -> None:
+        """Call after backward: reduces the stack-level grads and joins the communication stream."""
+        if self.world == 1:
+            return
+        rest = [p.grad for n, p in self.fusion.named_parameters() if not n.startswith("layers.") and p.grad is not None]
+        if rest:
+            flat = torch.cat([g.reshape(-1) for g in rest])
+            if self.average:
+                flat.div_(self.world)
+            dist.all_reduce(flat, group=self.pg)
+            o = 0
+            for g in rest:
+                g.copy_(flat[o:o + g.numel()].view_as(g))
+                o += g.numel()
+        for w in self.pending:
+            w.wait()                           # makes the current stream wait for the collective
+        if self.comm_stream is not None:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self.pending.clear()
+        self.buckets.clear()
+
+
+def shard_batch(global_batch: int, rank: int, world: int):
+    """Contiguous batch shard of rank `rank` (reference: DistributedSamplerWrapper, data_module.py:84-106)."""
+    per = global_batch // world
+    rem = global_batch % world
+    start = rank * per + min(rank, rem)
+    return start, start + per + (1 if rank < rem else 0)
