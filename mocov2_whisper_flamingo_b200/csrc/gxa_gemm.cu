@@ -236,6 +236,22 @@ static int launch_epi(const GemmOp& op, const GemmParams& p, cudaStream_t s) {
   return GXA_ERR_UNSUPPORTED;
 }
 
+int gemm2_launch(const GemmOp& op, const GemmParams& p, cudaStream_t s);
+
+// split-K factor for the atomically-accumulating fp32 epilogue: fill every SM (or SM pair) in whole waves
+static int pick_splits(int tiles, int workers, int kb_total) {
+  int best = 1;
+  double best_eff = 0.0;
+  for (int ks = 1; ks <= 16; ++ks) {
+    if (ks > 1 && kb_total / ks < 8) break;
+    const int units = tiles * ks;
+    const int waves = (units + workers - 1) / workers;
+    const double eff = double(units) / (double(waves) * workers);
+    if (eff > best_eff + 0.03) { best_eff = eff; best = ks; }
+  }
+  return best;
+}
+
 int gemm_launch(const GemmOp& op, cudaStream_t stream) {
   if (op.M <= 0 || op.N <= 0 || op.K <= 0) return GXA_ERR_SHAPE;
   if (op.N % 64 != 0) return GXA_ERR_SHAPE;
@@ -246,17 +262,21 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
   const int kb_total = (op.K + GEMM_BK - 1) / GEMM_BK;
   int bn = op.bn;
   if (bn == 0) {
-    // 256-wide tiles halve the A re-reads and the epilogue count; fall back to 128 when N does not
-    // divide or when the 256-wide grid would leave most SMs idle.
-    const int num_m = (op.M + GEMM_BM - 1) / GEMM_BM;
-    bn = (op.N % 256 == 0 && num_m * (op.N / 256) >= num_sms()) ? 256 : 128;
+    // CTA-pair 256x256 tiles for anything big; 1-CTA 128-wide tiles for small / narrow problems
+    if (op.M >= 512 && op.N >= 512 && (op.N % 256 == 0 || op.N >= 1024)) bn = 512;
+    else {
+      const int num_m = (op.M + GEMM_BM - 1) / GEMM_BM;
+      bn = (op.N % 256 == 0 && num_m * (op.N / 256) >= num_sms()) ? 256 : 128;
+    }
   }
+  const bool pair = bn == 512;
   int ks = op.k_splits;
   if (ks == 0) {
     ks = 1;
-    if (op.epi == EPI_F32) {   // wgrad: few output tiles, very long K -> split so that every SM has work
-      const int tiles = ((op.M + GEMM_BM - 1) / GEMM_BM) * ((op.N + bn - 1) / bn);
-      while (tiles * ks < num_sms() && ks < 8 && kb_total / (ks * 2) >= 8) ks *= 2;
+    if (op.epi == EPI_F32) {   // wgrad: few output tiles, very long K
+      const int tiles = pair ? ((op.M + 255) / 256) * ((op.N + 255) / 256)
+                             : ((op.M + GEMM_BM - 1) / GEMM_BM) * ((op.N + bn - 1) / bn);
+      ks = pick_splits(tiles, pair ? num_sms() / 2 : num_sms(), kb_total);
     }
   }
   while (ks > 1 && (ks - 1) * ((kb_total + ks - 1) / ks) >= kb_total) --ks;   // no empty split
@@ -271,6 +291,7 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
         return GXA_ERR_CUDA;
     }
   }
+  if (pair) return gemm2_launch(op, p, stream);
   if (bn == 256) return launch_epi<256>(op, p, stream);
   if (bn == 128) return launch_epi<128>(op, p, stream);
   return GXA_ERR_UNSUPPORTED;

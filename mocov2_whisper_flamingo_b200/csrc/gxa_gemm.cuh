@@ -146,4 +146,101 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
   }
 }
 
+
+// ---------------------------------------------------------------- epilogue v2 (coalesced)
+// The TMEM load gives each thread one ROW of a 32x32 fp32 chunk.  The warp transposes it through a
+// 4 KB XOR-swizzled staging buffer so that 8 lanes cover one 128-byte row segment: every global
+// load/store of the fused epilogue is then fully coalesced, and bias / gate are loaded once per lane.
+__device__ __forceinline__ float erf_fast(float x, float& e_out) {   // Abramowitz-Stegun 7.1.26, |err| <= 1.5e-7
+  const float ax = fabsf(x);
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, ax, 1.0f));
+  const float e = __expf(-ax * ax);
+  e_out = e;
+  float poly = fmaf(t, 1.061405429f, -1.453152027f);
+  poly = fmaf(t, poly, 1.421413741f);
+  poly = fmaf(t, poly, -0.284496736f);
+  poly = fmaf(t, poly, 0.254829592f);
+  const float y = fmaf(-poly * t, e, 1.0f);
+  return copysignf(y, x);
+}
+__device__ __forceinline__ float gelu_fast(float u) {
+  float e;
+  return 0.5f * u * (1.0f + erf_fast(u * 0.70710678118654752f, e));
+}
+__device__ __forceinline__ float gelu_grad_fast(float u) {
+  float e;   // e = exp(-(u/sqrt2)^2) = exp(-u^2/2)
+  const float cdf = 0.5f * (1.0f + erf_fast(u * 0.70710678118654752f, e));
+  return fmaf(u * 0.3989422804014327f, e, cdf);
+}
+__device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
+  uint2 r;
+  r.x = pack_bf16(v.x, v.y);
+  r.y = pack_bf16(v.z, v.w);
+  return r;
+}
+__device__ __forceinline__ float4 round_bf16x4(float4 v) {
+  return make_float4(bf16r(v.x), bf16r(v.y), bf16r(v.z), bf16r(v.w));
+}
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* stage, int row0, int col,
+                                                  const uint32_t (&r)[32], float gate_t, bool first_split, int lane) {
+  const uint32_t sbase = smem_u32(stage);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t a = sbase + lane * 128 + ((j ^ (lane & 7)) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(r[4 * j]), "r"(r[4 * j + 1]),
+                 "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                 : "memory");
+  }
+  __syncwarp();
+  const int cl = lane & 7, rsub = lane >> 3;
+  const int c = col + 4 * cl;
+  float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias != nullptr && first_split) b = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int rr = it * 4 + rsub;
+    const int row = row0 + rr;
+    float4 a;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w)
+                 : "r"(sbase + rr * 128 + ((cl ^ (rr & 7)) << 4)));
+    if (row >= p.M) continue;
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    const size_t off = static_cast<size_t>(row) * p.ldc + c;
+    if constexpr (EPI == EPI_BF16) {
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(a);
+    } else if constexpr (EPI == EPI_F32) {
+      float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + off);
+      if (p.accumulate || p.k_splits > 1) atomicAdd(dst, a);
+      else *dst = a;
+    } else if constexpr (EPI == EPI_GATE_RES) {
+      a = round_bf16x4(a);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) =
+          pack_bf16x4(a);
+      const float4 x = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) +
+                                                            static_cast<size_t>(row) * p.ld_aux + c));
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + off) =
+          make_float4(fmaf(gate_t, a.x, x.x), fmaf(gate_t, a.y, x.y), fmaf(gate_t, a.z, x.z), fmaf(gate_t, a.w, x.w));
+    } else if constexpr (EPI == EPI_BIAS_GELU) {
+      a = round_bf16x4(a);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(a);
+      const float4 g = make_float4(gelu_fast(a.x), gelu_fast(a.y), gelu_fast(a.z), gelu_fast(a.w));
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) =
+          pack_bf16x4(g);
+    } else if constexpr (EPI == EPI_GELU_BWD) {
+      a = round_bf16x4(a);
+      const uint2 uq = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
+                                                            static_cast<size_t>(row) * p.ld_aux + c));
+      const float2 u0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uq.x));
+      const float2 u1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uq.y));
+      const float4 o = make_float4(a.x * gelu_grad_fast(u0.x), a.y * gelu_grad_fast(u0.y), a.z * gelu_grad_fast(u1.x),
+                                   a.w * gelu_grad_fast(u1.y));
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(o);
+    }
+  }
+  __syncwarp();
+}
+
 }  // namespace gxa

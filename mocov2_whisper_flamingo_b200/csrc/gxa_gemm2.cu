@@ -1,0 +1,243 @@
+// 2-CTA (cta_group::2) tcgen05 GEMM: a CTA pair (cluster of 2 SMs of one TPC) computes one 256 x 256 tile.
+//
+// Why: with a 1-CTA 128x256 tile every 128-cycle MMA step reads 12 KB of smem while TMA writes another
+// 12 KB -- more than the 128 B/clk shared-memory port (ncu: tensor pipe 60 % active, profiles/r01_a_*).
+// In pair mode each CTA stages its own 128 rows of A and only HALF of B (128 of the 256 columns); the
+// tensor cores of both SMs consume both halves, so per-SM smem traffic drops by a third and L2->SM traffic
+// per FLOP drops from 1/85 to 1/128 B/FLOP.
+//
+//   warp 8 (both CTAs)  : TMA producer for its CTA's A rows / B half; bytes complete on the LEADER's barrier
+//   warp 9 (leader only): issues tcgen05.mma.cta_group::2, commits multicast to both CTAs' barriers
+//   warps 0-7 (both)    : epilogue of the CTA's own 128 x 256 accumulator (TMEM -> smem transpose -> coalesced HBM)
+#include "gxa_gemm.cuh"
+#include "gxa_host.h"
+
+namespace gxa {
+
+constexpr int G2_BM = 256;        // per pair
+constexpr int G2_BN = 256;
+constexpr int G2_STAGES = 5;
+constexpr int G2_A_BYTES = 128 * GEMM_BK * 2;      // this CTA's 128 rows of A
+constexpr int G2_B_BYTES = 128 * GEMM_BK * 2;      // this CTA's 128 columns of B
+constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_B_BYTES;
+constexpr int G2_EPI_STAGE_BYTES = GEMM_EPI_WARPS * 4096;
+constexpr int G2_SMEM_BYTES = G2_STAGES * G2_STAGE_BYTES + G2_EPI_STAGE_BYTES + 1024 + 256;
+constexpr int G2_TMEM_COLS = 512;
+
+template <int EPI, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* epi_stage = smem + G2_STAGES * G2_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_stage + G2_EPI_STAGE_BYTES);
+  uint64_t* full = bars;                    // [STAGES] used in the leader CTA only
+  uint64_t* empty = bars + G2_STAGES;       // [STAGES] one per CTA, signalled by the leader's multicast commit
+  uint64_t* tfull = bars + 2 * G2_STAGES;   // [2] one per CTA (multicast commit)
+  uint64_t* tempty = tfull + 2;             // [2] leader only: 16 arrivals (8 epilogue warps x 2 CTAs)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+
+  const int num_m = (p.M + G2_BM - 1) / G2_BM;
+  const int num_n = (p.N + G2_BN - 1) / G2_BN;
+  const int kb_total = (p.K + GEMM_BK - 1) / GEMM_BK;
+  const int kb_per = (kb_total + p.k_splits - 1) / p.k_splits;
+  const int total = num_m * num_n * p.k_splits;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < G2_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 2 * GEMM_EPI_WARPS);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 9) tmem_alloc_pair(tmem_slot, G2_TMEM_COLS);
+  tc_fence_before();
+  cluster_sync_all();                 // barrier inits + TMEM allocation visible in both CTAs
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 8) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = pair; w < total; w += num_pairs) {
+        const int split = w % p.k_splits;
+        const int tile = w / p.k_splits;
+        const int m0 = (tile / num_n) * G2_BM + rank * 128;
+        const int n0 = (tile % num_n) * G2_BN + rank * 128;
+        const int kb0 = split * kb_per;
+        const int kb1 = min(kb_total, kb0 + kb_per);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sA = smem + stage * G2_STAGE_BYTES;
+          uint8_t* sB = sA + G2_A_BYTES;
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);   // bytes of BOTH CTAs
+          if constexpr (!A_MN) {
+            tma_load_2d_pair(sA, &tmA, &full[stage], kb * GEMM_BK, m0);
+          } else {
+            tma_load_2d_pair(sA, &tmA, &full[stage], m0, kb * GEMM_BK);
+            tma_load_2d_pair(sA + 8192, &tmA, &full[stage], m0 + 64, kb * GEMM_BK);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_pair(sB, &tmB, &full[stage], kb * GEMM_BK, n0);
+          } else {
+            tma_load_2d_pair(sB, &tmB, &full[stage], n0, kb * GEMM_BK);
+            tma_load_2d_pair(sB + 8192, &tmB, &full[stage], n0 + 64, kb * GEMM_BK);
+          }
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (leader) {
+      constexpr uint32_t idesc = umma_idesc_bf16(G2_BM, G2_BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int w = pair; w < total; w += num_pairs) {
+        const int split = w % p.k_splits;
+        const int kb0 = split * kb_per;
+        const int kb1 = min(kb_total, kb0 + kb_per);
+        mbar_wait(&tempty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * G2_BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t a_base = smem_u32(smem + stage * G2_STAGE_BYTES);
+            const uint32_t b_base = a_base + G2_A_BYTES;
+#pragma unroll
+            for (int k = 0; k < GEMM_BK / 16; ++k) {
+              const uint64_t da = A_MN ? umma_desc_sw128(a_base + k * 2048, 8192, 1024)
+                                       : umma_desc_sw128(a_base + k * 32, 16, 1024);
+              const uint64_t db = B_MN ? umma_desc_sw128(b_base + k * 2048, 8192, 1024)
+                                       : umma_desc_sw128(b_base + k * 32, 16, 1024);
+              umma_bf16_pair(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit_pair(&empty[stage], 3);     // frees this smem slot in BOTH CTAs
+          }
+          __syncwarp();
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        if (lane == 0) umma_commit_pair(&tfull[as], 3);   // accumulator ready in both CTAs
+        __syncwarp();
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue warps 0..7 (both CTAs)
+    const int quarter = warp & 3;
+    const int half = warp >> 2;
+    uint8_t* stage_buf = epi_stage + warp * 4096;
+    float gate_t = 0.f;
+    if constexpr (EPI == EPI_GATE_RES) gate_t = tanhf(__ldg(p.gate));
+    const uint32_t tempty_leader0 = mapa_shared(smem_u32(&tempty[0]), 0);
+    const uint32_t tempty_leader1 = mapa_shared(smem_u32(&tempty[1]), 0);
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int w = pair; w < total; w += num_pairs) {
+      const int split = w % p.k_splits;
+      const int tile = w / p.k_splits;
+      const int m0 = (tile / num_n) * G2_BM + rank * 128;
+      const int n0 = (tile % num_n) * G2_BN;
+      mbar_wait(&tfull[as], aphase);
+      tc_fence_after();
+      const int row0 = m0 + quarter * 32;
+#pragma unroll 1
+      for (int c = half * (G2_BN / 2); c < (half + 1) * (G2_BN / 2); c += 32) {
+        if (n0 + c >= p.N) break;
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * G2_BN + c, r);
+        tmem_ld_wait();
+        epilogue_chunk_v2<EPI>(p, stage_buf, row0, n0 + c, r, gate_t, split == 0, lane);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(as == 0 ? tempty_leader0 : tempty_leader1);
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncwarp();
+  cluster_sync_all();                 // nobody exits (or frees TMEM) while the peer may still signal / read
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, G2_TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------ host side
+int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                   uint32_t box_outer);
+
+template <int EPI, bool A_MN, bool B_MN>
+static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stream) {
+  CUtensorMap tmA, tmB;
+  int e;
+  if (!A_MN) e = make_tmap_bf16(&tmA, op.A, op.K, op.M, op.lda, GEMM_BK, 128);
+  else       e = make_tmap_bf16(&tmA, op.A, op.M, op.K, op.lda, 64, GEMM_BK);
+  if (e) return e;
+  if (!B_MN) e = make_tmap_bf16(&tmB, op.B, op.K, op.N, op.ldb, GEMM_BK, 128);
+  else       e = make_tmap_bf16(&tmB, op.B, op.N, op.K, op.ldb, 64, GEMM_BK);
+  if (e) return e;
+  auto kern = gemm_tc2_kernel<EPI, A_MN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES) != cudaSuccess)
+      return GXA_ERR_CUDA;
+    attr_set = true;
+  }
+  const int num_m = (p.M + G2_BM - 1) / G2_BM, num_n = (p.N + G2_BN - 1) / G2_BN;
+  const int total = num_m * num_n * p.k_splits;
+  const int max_pairs = num_sms() / 2;
+  const int pairs = total < max_pairs ? total : max_pairs;
+  kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(tmA, tmB, p);
+  count_launch();
+  return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
+}
+
+template <int EPI>
+static int launch2_layout(const GemmOp& op, const GemmParams& p, cudaStream_t s) {
+  if (!op.a_mn && !op.b_mn) return launch2_inst<EPI, false, false>(op, p, s);
+  if (!op.a_mn && op.b_mn) return launch2_inst<EPI, false, true>(op, p, s);
+  if constexpr (EPI == EPI_F32) {
+    if (op.a_mn && op.b_mn) return launch2_inst<EPI, true, true>(op, p, s);
+    if (op.a_mn && !op.b_mn) return launch2_inst<EPI, true, false>(op, p, s);
+  }
+  return GXA_ERR_UNSUPPORTED;
+}
+
+int gemm2_launch(const GemmOp& op, const GemmParams& p, cudaStream_t s) {
+  switch (op.epi) {
+    case EPI_BF16: return launch2_layout<EPI_BF16>(op, p, s);
+    case EPI_F32: return launch2_layout<EPI_F32>(op, p, s);
+    case EPI_GATE_RES: return launch2_layout<EPI_GATE_RES>(op, p, s);
+    case EPI_BIAS_GELU: return launch2_layout<EPI_BIAS_GELU>(op, p, s);
+    case EPI_GELU_BWD: return launch2_layout<EPI_GELU_BWD>(op, p, s);
+  }
+  return GXA_ERR_UNSUPPORTED;
+}
+
+}  // namespace gxa

@@ -92,3 +92,53 @@ def test_epilogue_bias_gelu_and_backward():
     u = U.float().requires_grad_(True)
     torch.nn.functional.gelu(u).backward(dA)
     assert rel_err(dU.float(), u.grad) < 1e-2
+
+
+# ---- CTA-pair (cta_group::2) 256x256 kernel, selected with bn=512 ---------------------------------
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (256, 256, 512), (1000, 1536, 200), (896, 384, 1024),
+                                   (3000, 1024, 520), (4096, 4096, 1024)])
+def test_pair_kernel_layouts_f32(a_mn, b_mn, M, N, K):
+    if (a_mn and M % 8) or (b_mn and N % 8):
+        pytest.skip("row pitch not 16-byte aligned for this layout")
+    A, B = operands(M, N, K, seed=7)
+    Cm, _ = gemm(A, B, a_mn, b_mn, bn=512)
+    R = ref_mm(A, B)
+    e = rel_err(Cm, R)
+    assert e < TOL, f"rel err {e:.3e}\n{err_map(Cm, R)}"
+
+
+@pytest.mark.parametrize("ks", [1, 2, 5])
+def test_pair_kernel_split_k_accumulate(ks):
+    A, B = operands(1024, 512, 3000, seed=8)
+    R = ref_mm(A, B)
+    C0 = torch.randn(1024, 512, device="cuda")
+    Cm, _ = gemm(A, B, True, True, accumulate=1, C_init=C0, k_splits=ks, bn=512)
+    assert rel_err(Cm, R + C0) < TOL
+
+
+def test_pair_kernel_epilogues():
+    A, B = operands(700, 1536, 384, seed=9)
+    bias = torch.randn(1536, device="cuda")
+    Cm, _ = gemm(A, B, epi=_lib.EPI_BF16, bias=bias, bn=512)
+    R = (ref_mm(A, B) + bias).to(torch.bfloat16)
+    assert rel_err(Cm.float(), R.float()) < 8e-3
+    U, Act = gemm(A, B, epi=_lib.EPI_BIAS_GELU, bias=bias, bn=512)
+    assert rel_err(U.float(), R.float()) < 8e-3
+    a_ref = torch.nn.functional.gelu(U.float()).to(torch.bfloat16)
+    assert rel_err(Act.float(), a_ref.float()) < 8e-3
+    assert (Act.float() - a_ref.float()).abs().max() < 2e-2 * a_ref.float().abs().max()
+    dF, W2t = operands(700, 1536, 384, seed=10)
+    dU, _ = gemm(dF, W2t, False, True, epi=_lib.EPI_GELU_BWD, aux=U, bn=512)
+    dA = ref_mm(dF, W2t).to(torch.bfloat16).float()
+    u = U.float().requires_grad_(True)
+    torch.nn.functional.gelu(u).backward(dA)
+    assert rel_err(dU.float(), u.grad) < 1e-2
+    A2, B2 = operands(700, 512, 1536, seed=11)
+    b2 = torch.randn(512, device="cuda")
+    X = torch.randn(700, 512, device="cuda")
+    gate = torch.tensor([-0.4], device="cuda")
+    Y, O = gemm(A2, B2, epi=_lib.EPI_GATE_RES, bias=b2, aux=X, gate=gate, bn=512)
+    o_ref = (ref_mm(A2, B2) + b2).to(torch.bfloat16)
+    assert rel_err(O.float(), o_ref.float()) < 8e-3
+    assert rel_err(Y, X + math.tanh(-0.4) * O.float()) < 1e-6
