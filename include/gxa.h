@@ -136,9 +136,13 @@ int gxa_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int 
  * [64h, 64h+64)); ctx: bf16 [B*Lq, ldc]; lse: fp32 [B, H, Lq] (natural log). */
 int gxa_attn_fwd(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
                  const int32_t* kv_end, void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, void* stream);
+/* workspace: gxa_attn_bwd_workspace_bytes() of scratch (fp32 dQ accumulator of the tcgen05 path); NULL selects the
+ * scratch-free legacy kernels. */
+size_t gxa_attn_bwd_workspace_bytes(int B, int H, int Lq);
 int gxa_attn_bwd(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
                  const int32_t* kv_end, const void* ctx, const void* dctx, int ldc, const float* lse, float* delta,
-                 void* dq, int lddq, void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, void* stream);
+                 void* dq, int lddq, void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk,
+                 void* stream);
 
 #ifdef __cplusplus
 }

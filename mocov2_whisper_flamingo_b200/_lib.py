@@ -55,8 +55,9 @@ SIGNATURES = {
     "gxa_gemm_bf16": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i,
                            _vp]),
     "gxa_attn_fwd": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp]),
-    "gxa_attn_bwd": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i,
-                          _vp]),
+    "gxa_attn_bwd_workspace_bytes": (_sz, [_i, _i, _i]),
+    "gxa_attn_bwd": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i,
+                          _i, _vp]),
 }
 
 _lib = None

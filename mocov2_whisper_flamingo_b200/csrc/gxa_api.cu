@@ -72,6 +72,7 @@ struct SavedBf16 {
 struct WorkBf16 {
   float *gacc, *dx1, *delta;
   bf16 *df, *du, *dh2, *dob, *dctx, *dq, *dkv, *dh;
+  float* dqacc;
   size_t bytes;
   WorkBf16(const gxa_dims& d, void* base) {
     const size_t M = size_t(d.B) * d.Lq, Mk = size_t(d.B) * d.Lk, D = d.D;
@@ -81,6 +82,7 @@ struct WorkBf16 {
     delta = c.take<float>(size_t(d.B) * d.H * d.Lq);
     df = c.take<bf16>(M * D); du = c.take<bf16>(M * 4 * D); dh2 = c.take<bf16>(M * D); dob = c.take<bf16>(M * D);
     dctx = c.take<bf16>(M * D); dq = c.take<bf16>(M * D); dkv = c.take<bf16>(Mk * 2 * D); dh = c.take<bf16>(M * D);
+    dqacc = c.take<float>(attn_bwd_workspace_bytes(d.B, d.H, d.Lq) / sizeof(float));
     bytes = c.off;
   }
 };
@@ -253,7 +255,7 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
                     nullptr, 1, s));
   // ---- attention core
   GXA_TRY(attn_bwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, Wk.dctx, D, S.lse, Wk.delta, Wk.dq, D,
-                        Wk.dkv, Wk.dkv + D, 2 * D, d.B, d.H, d.Lq, d.Lk, s));
+                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s));
   GXA_TRY(colsum(Wk.dq, 0, D, g.in_proj_b, M, D, s));
   GXA_TRY(colsum(Wk.dkv, 0, 2 * D, g.in_proj_b + D, Mk, 2 * D, s));
   GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
@@ -500,12 +502,15 @@ int gxa_attn_fwd(const void* q, int ldq, const void* k, const void* v, int ldkv,
                         reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
+size_t gxa_attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_workspace_bytes(B, H, Lq); }
+
 int gxa_attn_bwd(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
                  const int32_t* kv_end, const void* ctx, const void* dctx, int ldc, const float* lse, float* delta,
-                 void* dq, int lddq, void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, void* stream) {
+                 void* dq, int lddq, void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk,
+                 void* stream) {
   if (!q || !k || !v || !ctx || !dctx || !lse || !delta || !dq || !dk || !dv) return GXA_ERR_ARG;
-  GXA_TRY(attn_bwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, dctx, ldc, lse, delta, dq, lddq, dk, dv, lddkv, B, H, Lq,
-                        Lk, reinterpret_cast<cudaStream_t>(stream)));
+  GXA_TRY(attn_bwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, dctx, ldc, lse, delta, dq, lddq, dk, dv, lddkv, workspace,
+                        B, H, Lq, Lk, reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
 

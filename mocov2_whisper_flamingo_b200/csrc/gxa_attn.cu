@@ -8,6 +8,8 @@
 //   backward: dK/dV kernel (CTA = 64 keys, loops over query tiles, works on S^T so that no
 //             register/smem transposes are needed) + dQ kernel (CTA = 64 queries, loops over key tiles).
 //             Deterministic: no atomics.
+#include <cstdlib>
+
 #include "gxa_host.h"
 
 namespace gxa {
@@ -410,10 +412,27 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, int ldq, const __nv_bflo
 // ================================================================== host launchers
 static inline int chk() { count_launch(); return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA; }
 
+int attn_fwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end, void* ctx,
+                int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s);
+
+// GXA_ATTN=legacy selects the mma.sync kernels (A/B comparison); default is the tcgen05 path
+static bool use_legacy_attn() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GXA_ATTN");
+    v = (e && e[0] == 'l') ? 1 : 0;
+  }
+  return v == 1;
+}
+
 int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s) {
   if (B <= 0 || H <= 0 || Lq <= 0 || Lk <= 0) return GXA_ERR_SHAPE;
   if ((ldq % 8) || (ldkv % 8) || (ldc % 8)) return GXA_ERR_ALIGN;
+  // tcgen05 path: K|V packed side by side in one [B*Lk, 2D] matrix (the KV projection's natural output)
+  if (!use_legacy_attn() && Lk <= 1024 && ldkv == 2 * H * 64 &&
+      v == reinterpret_cast<const __nv_bfloat16*>(k) + H * 64 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0)
+    return attn_fwd_tc(q, ldq, k, ldkv, mask, kv_end, ctx, ldc, lse, B, H, Lq, Lk, s);
   dim3 grid((Lq + AT - 1) / AT, H, B);
   attn_fwd_kernel<<<grid, ATT_THREADS, 0, s>>>(
       reinterpret_cast<const __nv_bfloat16*>(q), ldq, reinterpret_cast<const __nv_bfloat16*>(k),
@@ -422,9 +441,16 @@ int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
   return chk();
 }
 
+int attn_bwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
+                const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
+                void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
+size_t attn_bwd_tc_workspace(int B, int H, int Lq);
+
+size_t attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_tc_workspace(B, H, Lq); }
+
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
-                  void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s) {
+                  void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s) {
   if (B <= 0 || H <= 0 || Lq <= 0 || Lk <= 0) return GXA_ERR_SHAPE;
   if ((ldq % 8) || (ldkv % 8) || (ldc % 8) || (lddq % 8) || (lddkv % 8)) return GXA_ERR_ALIGN;
   auto Q = reinterpret_cast<const __nv_bfloat16*>(q);
@@ -434,6 +460,11 @@ int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
   attn_delta_kernel<<<(B * Lq + 7) / 8, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(ctx), dO, ldc, delta, B, H,
                                                      Lq);
   if (int e = chk()) return e;
+  // tcgen05 path: K|V (and dK|dV) packed side by side, scratch for the fp32 dQ accumulator available
+  if (!use_legacy_attn() && workspace != nullptr && Lk <= 1024 && Lq <= 1024 && ldkv == 2 * H * 64 && lddkv == ldkv &&
+      V == K + H * 64 && reinterpret_cast<__nv_bfloat16*>(dv) == reinterpret_cast<__nv_bfloat16*>(dk) + H * 64)
+    return attn_bwd_tc(q, ldq, k, ldkv, mask, kv_end, dctx, ldc, lse, delta, reinterpret_cast<float*>(workspace), dq,
+                       lddq, dk, dv, lddkv, B, H, Lq, Lk, s);
   static bool attr = false;
   if (!attr) {
     if (cudaFuncSetAttribute(attn_bwd_dkv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -187,6 +187,22 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t ou
   return r == CUDA_SUCCESS ? 0 : GXA_ERR_TMAP;
 }
 
+
+// 3-D bf16 tensor map [d2][d1][d0] (d0 contiguous): box {b0, b1, 1}, 128B swizzle, OOB rows read as zero.
+int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t ld1,
+                      uint64_t ld2, uint32_t b0, uint32_t b1) {
+  if (int e = get_encode()) return e;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld1 * 2) % 16 || (ld2 * 2) % 16) return GXA_ERR_ALIGN;
+  cuuint64_t dims[3] = {d0, d1, d2};
+  cuuint64_t strides[2] = {ld1 * 2, ld2 * 2};
+  cuuint32_t box[3] = {b0, b1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : GXA_ERR_TMAP;
+}
+
 template <int BN, int EPI, bool A_MN, bool B_MN>
 static int launch_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;

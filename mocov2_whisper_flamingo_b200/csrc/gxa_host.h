@@ -33,6 +33,10 @@ struct GemmOp {
   int k_splits = 0;  // 0 = choose
 };
 int gemm_launch(const GemmOp& op, cudaStream_t stream);
+int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                   uint32_t box_outer);
+int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t ld1,
+                      uint64_t ld2, uint32_t b0, uint32_t b1);
 
 // ---- row-wise / elementwise kernels (gxa_rowwise.cu)
 int ln_fwd(const float* x, const float* w, const float* b, void* out, int out_is_f32, float* mean, float* rstd, int rows,
@@ -63,7 +67,8 @@ int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
                   void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s);
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
-                  void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
+                  void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s);
+size_t attn_bwd_workspace_bytes(int B, int H, int Lq);
 int attn_fwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const uint8_t* mask, float* ctx,
                  int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s);
 int attn_bwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const float* dctx, int ldc,

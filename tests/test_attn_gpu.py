@@ -53,8 +53,9 @@ def run(B, H, Lq, Lk, lengths, seed=0, garbage=True):
     dq = torch.full_like(q, float("nan"))
     dkv = torch.full_like(kv, float("nan"))
     delta = torch.empty(B, H, Lq, device="cuda")
+    wsb = torch.empty(L.gxa_attn_bwd_workspace_bytes(B, H, Lq), dtype=torch.uint8, device="cuda")
     _lib.check(L.gxa_attn_bwd(ptr(q), D, ptr(k), ptr(v), 2 * D, ptr(m8), ptr(kvend), ptr(ctx), ptr(dctx), D, ptr(lse),
-                              ptr(delta), ptr(dq), D, ptr(dkv), ptr(dkv[..., D:]), 2 * D, B, H, Lq, Lk, stream()),
+                              ptr(delta), ptr(dq), D, ptr(dkv), ptr(dkv[..., D:]), 2 * D, ptr(wsb), B, H, Lq, Lk, stream()),
                "attn_bwd")
     torch.cuda.synchronize()
     qr, kr, vr = (t.float().clone().requires_grad_(True) for t in (q, k, v))
