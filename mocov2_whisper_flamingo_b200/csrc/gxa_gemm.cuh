@@ -151,40 +151,97 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 // The TMEM load gives each thread one ROW of a 32x32 fp32 chunk.  The warp transposes it through a
 // 4 KB XOR-swizzled staging buffer so that 8 lanes cover one 128-byte row segment: every global
 // load/store of the fused epilogue is then fully coalesced, and bias / gate are loaded once per lane.
-__device__ __forceinline__ float erf_fast(float x, float& e_out) {   // Abramowitz-Stegun 7.1.26, |err| <= 1.5e-7
-  const float ax = fabsf(x);
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, ax, 1.0f));
-  const float e = __expf(-ax * ax);
-  e_out = e;
-  float poly = fmaf(t, 1.061405429f, -1.453152027f);
-  poly = fmaf(t, poly, 1.421413741f);
-  poly = fmaf(t, poly, -0.284496736f);
-  poly = fmaf(t, poly, 0.254829592f);
-  const float y = fmaf(-poly * t, e, 1.0f);
-  return copysignf(y, x);
+// erf-GELU on packed f32x2 (FFMA2/FMUL2 on sm_100 halve the issue slots of the polynomial).
+//   Phi(u) = 0.5*erfc(-u/sqrt2);  Abramowitz-Stegun 7.1.26:  0.5*erfc(z) = hh(t)*exp(-z^2),  t = 1/(1 + p z),  z = |u|/sqrt2
+//   gelu(u)  = relu(u) - |u| * h(|u|)            h = hh(t) * exp(-u^2/2)   (|err| <= 1e-7 on Phi)
+//   gelu'(u) = 0.5 + copysign(0.5 - h, u) + u * phi0 * exp(-u^2/2)
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
-__device__ __forceinline__ float gelu_fast(float u) {
-  float e;
-  return 0.5f * u * (1.0f + erf_fast(u * 0.70710678118654752f, e));
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
-__device__ __forceinline__ float gelu_grad_fast(float u) {
-  float e;   // e = exp(-(u/sqrt2)^2) = exp(-u^2/2)
-  const float cdf = 0.5f * (1.0f + erf_fast(u * 0.70710678118654752f, e));
-  return fmaf(u * 0.3989422804014327f, e, cdf);
+__device__ __forceinline__ float2 f2(float a) { return make_float2(a, a); }
+// returns -h(|u|) and e = exp(-u^2/2)
+__device__ __forceinline__ float2 gelu_neg_h2(float2 u, float2 au, float2& e) {
+  const float2 d = __ffma2_rn(au, f2(0.3275911f * 0.70710678118654752f), f2(1.0f));
+  const float2 t = make_float2(rcp_approx(d.x), rcp_approx(d.y));
+  const float2 w = __fmul2_rn(__fmul2_rn(u, f2(-0.5f * 1.4426950408889634f)), u);
+  e = make_float2(ex2_approx(w.x), ex2_approx(w.y));
+  float2 poly = __ffma2_rn(t, f2(-0.5f * 1.061405429f), f2(0.5f * 1.453152027f));
+  poly = __ffma2_rn(t, poly, f2(-0.5f * 1.421413741f));
+  poly = __ffma2_rn(t, poly, f2(0.5f * 0.284496736f));
+  poly = __ffma2_rn(t, poly, f2(-0.5f * 0.254829592f));
+  return __fmul2_rn(__fmul2_rn(poly, t), e);
 }
+__device__ __forceinline__ float2 gelu_fast2(float2 u) {
+  const float2 au = make_float2(fabsf(u.x), fabsf(u.y));
+  float2 e;
+  const float2 nh = gelu_neg_h2(u, au, e);
+  return __ffma2_rn(au, nh, make_float2(fmaxf(u.x, 0.f), fmaxf(u.y, 0.f)));
+}
+__device__ __forceinline__ float2 gelu_grad_fast2(float2 u) {
+  const float2 au = make_float2(fabsf(u.x), fabsf(u.y));
+  float2 e;
+  const float2 nh = gelu_neg_h2(u, au, e);
+  const float2 q = __fadd2_rn(nh, f2(0.5f));                        // 0.5 - h >= 0
+  const float2 cdf = __fadd2_rn(make_float2(copysignf(q.x, u.x), copysignf(q.y, u.y)), f2(0.5f));
+  return __ffma2_rn(__fmul2_rn(u, f2(0.3989422804014327f)), e, cdf);
+}
+__device__ __forceinline__ float gelu_fast(float u) { return gelu_fast2(make_float2(u, u)).x; }
+__device__ __forceinline__ float gelu_grad_fast(float u) { return gelu_grad_fast2(make_float2(u, u)).x; }
 __device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
   uint2 r;
   r.x = pack_bf16(v.x, v.y);
   r.y = pack_bf16(v.z, v.w);
   return r;
 }
-__device__ __forceinline__ float4 round_bf16x4(float4 v) {
-  return make_float4(bf16r(v.x), bf16r(v.y), bf16r(v.z), bf16r(v.w));
+__device__ __forceinline__ float4 unpack_bf16x4(uint2 q) {
+  return make_float4(__uint_as_float(q.x << 16), __uint_as_float(q.x & 0xffff0000u), __uint_as_float(q.y << 16),
+                     __uint_as_float(q.y & 0xffff0000u));
+}
+__device__ __forceinline__ float4 round_bf16x4(float4 v) { return unpack_bf16x4(pack_bf16x4(v)); }
+
+// Per-lane operands of one 32x32 chunk that come from HBM (x for the gated residual, u for gelu'): fetched one
+// chunk AHEAD of their use so the load latency overlaps the previous chunk's TMEM read + math (the loads used to
+// be issued one by one inside the row loop: 8 exposed HBM round trips per chunk).
+template <int EPI>
+struct AuxRegs {};
+template <>
+struct AuxRegs<EPI_GATE_RES> { float4 v[8]; };
+template <>
+struct AuxRegs<EPI_GELU_BWD> { uint2 v[8]; };
+
+template <int EPI>
+__device__ __forceinline__ void aux_prefetch(const GemmParams& p, int row0, int col, int lane, AuxRegs<EPI>& ax) {
+  if constexpr (EPI == EPI_GATE_RES || EPI == EPI_GELU_BWD) {
+    const int c = col + 4 * (lane & 7), rsub = lane >> 3;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int row = row0 + it * 4 + rsub;
+      if constexpr (EPI == EPI_GATE_RES) {
+        ax.v[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < p.M)
+          ax.v[it] = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) +
+                                                          static_cast<size_t>(row) * p.ld_aux + c));
+      } else {
+        ax.v[it] = make_uint2(0u, 0u);
+        if (row < p.M)
+          ax.v[it] = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
+                                                         static_cast<size_t>(row) * p.ld_aux + c));
+      }
+    }
+  }
 }
 
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* stage, int row0, int col,
-                                                  const uint32_t (&r)[32], float gate_t, bool first_split, int lane) {
+                                                  const uint32_t (&r)[32], float gate_t, bool first_split, int lane,
+                                                  const AuxRegs<EPI>& ax) {
   const uint32_t sbase = smem_u32(stage);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -216,28 +273,25 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
       if (p.accumulate || p.k_splits > 1) atomicAdd(dst, a);
       else *dst = a;
     } else if constexpr (EPI == EPI_GATE_RES) {
-      a = round_bf16x4(a);
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) =
-          pack_bf16x4(a);
-      const float4 x = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) +
-                                                            static_cast<size_t>(row) * p.ld_aux + c));
+      const uint2 pk = pack_bf16x4(a);
+      a = unpack_bf16x4(pk);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) = pk;
+      const float4 x = ax.v[it];
       *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + off) =
           make_float4(fmaf(gate_t, a.x, x.x), fmaf(gate_t, a.y, x.y), fmaf(gate_t, a.z, x.z), fmaf(gate_t, a.w, x.w));
     } else if constexpr (EPI == EPI_BIAS_GELU) {
-      a = round_bf16x4(a);
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(a);
-      const float4 g = make_float4(gelu_fast(a.x), gelu_fast(a.y), gelu_fast(a.z), gelu_fast(a.w));
+      const uint2 pk = pack_bf16x4(a);
+      a = unpack_bf16x4(pk);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pk;
+      const float2 g0 = gelu_fast2(make_float2(a.x, a.y)), g1 = gelu_fast2(make_float2(a.z, a.w));
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) =
-          pack_bf16x4(g);
+          pack_bf16x4(make_float4(g0.x, g0.y, g1.x, g1.y));
     } else if constexpr (EPI == EPI_GELU_BWD) {
       a = round_bf16x4(a);
-      const uint2 uq = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
-                                                            static_cast<size_t>(row) * p.ld_aux + c));
-      const float2 u0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uq.x));
-      const float2 u1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uq.y));
-      const float4 o = make_float4(a.x * gelu_grad_fast(u0.x), a.y * gelu_grad_fast(u0.y), a.z * gelu_grad_fast(u1.x),
-                                   a.w * gelu_grad_fast(u1.y));
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(o);
+      const float4 u = unpack_bf16x4(ax.v[it]);
+      const float2 g0 = gelu_grad_fast2(make_float2(u.x, u.y)), g1 = gelu_grad_fast2(make_float2(u.z, u.w));
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) =
+          pack_bf16x4(make_float4(a.x * g0.x, a.y * g0.y, a.z * g1.x, a.w * g1.y));
     }
   }
   __syncwarp();

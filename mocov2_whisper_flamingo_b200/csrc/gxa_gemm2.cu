@@ -155,21 +155,40 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t tempty_leader1 = mapa_shared(smem_u32(&tempty[1]), 0);
     int as = 0;
     uint32_t aphase = 0;
+    constexpr int CHUNKS = G2_BN / 2 / 32;           // 32-column chunks per warp per tile
+    AuxRegs<EPI> ax[2];                              // chunk operands from HBM, fetched one chunk ahead
+    auto tile_origin = [&](int w, int& row0, int& n0) {
+      const int tile = w / p.k_splits;
+      row0 = (tile / num_n) * G2_BM + rank * 128 + quarter * 32;
+      n0 = (tile % num_n) * G2_BN + half * (G2_BN / 2);
+    };
+    if (pair < total) {
+      int r0, n0;
+      tile_origin(pair, r0, n0);
+      if (n0 < p.N) aux_prefetch<EPI>(p, r0, n0, lane, ax[0]);
+    }
     for (int w = pair; w < total; w += num_pairs) {
       const int split = w % p.k_splits;
-      const int tile = w / p.k_splits;
-      const int m0 = (tile / num_n) * G2_BM + rank * 128;
-      const int n0 = (tile % num_n) * G2_BN;
+      int row0, n0;
+      tile_origin(w, row0, n0);
       mbar_wait(&tfull[as], aphase);
       tc_fence_after();
-      const int row0 = m0 + quarter * 32;
-#pragma unroll 1
-      for (int c = half * (G2_BN / 2); c < (half + 1) * (G2_BN / 2); c += 32) {
-        if (n0 + c >= p.N) break;
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * G2_BN + c, r);
-        tmem_ld_wait();
-        epilogue_chunk_v2<EPI>(p, stage_buf, row0, n0 + c, r, gate_t, split == 0, lane);
+#pragma unroll
+      for (int ci = 0; ci < CHUNKS; ++ci) {
+        const int col = n0 + ci * 32;
+        if (ci + 1 < CHUNKS) {
+          if (col + 32 < p.N) aux_prefetch<EPI>(p, row0, col + 32, lane, ax[(ci + 1) & 1]);
+        } else if (w + num_pairs < total) {
+          int r1, n1;
+          tile_origin(w + num_pairs, r1, n1);
+          if (n1 < p.N) aux_prefetch<EPI>(p, r1, n1, lane, ax[0]);
+        }
+        if (col < p.N) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * G2_BN + half * (G2_BN / 2) + ci * 32, r);
+          tmem_ld_wait();
+          epilogue_chunk_v2<EPI>(p, stage_buf, row0, col, r, gate_t, split == 0, lane, ax[ci & 1]);
+        }
       }
       tc_fence_before();
       __syncwarp();
