@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libgxa_b200.so")
-SOURCES = ["gxa_gemm.cu", "gxa_gemm2.cu", "gxa_rowwise.cu", "gxa_attn.cu", "gxa_attn_tc.cu", "gxa_attn_f32.cu", "gxa_api.cu"]
+SOURCES = ["gxa_gemm.cu", "gxa_gemm2.cu", "gxa_rowwise.cu", "gxa_attn.cu", "gxa_attn_tc.cu", "gxa_attn_bwd_tc.cu", "gxa_attn_f32.cu", "gxa_api.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC"]

@@ -444,6 +444,9 @@ int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
 int attn_bwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
                 const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
+int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
+                 const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
+                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
 size_t attn_bwd_tc_workspace(int B, int H, int Lq);
 
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_tc_workspace(B, H, Lq); }
@@ -461,8 +464,13 @@ int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
                                                      Lq);
   if (int e = chk()) return e;
   // tcgen05 path: K|V (and dK|dV) packed side by side, scratch for the fp32 dQ accumulator available
-  if (!use_legacy_attn() && workspace != nullptr && Lk <= 1024 && Lq <= 1024 && ldkv == 2 * H * 64 && lddkv == ldkv &&
-      V == K + H * 64 && reinterpret_cast<__nv_bfloat16*>(dv) == reinterpret_cast<__nv_bfloat16*>(dk) + H * 64)
+  const bool packed = workspace != nullptr && ldkv == 2 * H * 64 && lddkv == ldkv && V == K + H * 64 &&
+                      reinterpret_cast<__nv_bfloat16*>(dv) == reinterpret_cast<__nv_bfloat16*>(dk) + H * 64;
+  static const bool bwd_v1 = getenv("GXA_ATTN_BWD") && getenv("GXA_ATTN_BWD")[0] == '1';   // A/B: per-item CTAs
+  if (!use_legacy_attn() && packed && !bwd_v1)       // persistent tcgen05 kernel (any Lq, Lk)
+    return attn_bwd_tc2(q, ldq, k, ldkv, mask, kv_end, dctx, ldc, lse, delta, reinterpret_cast<float*>(workspace), dq,
+                        lddq, dk, dv, lddkv, B, H, Lq, Lk, s);
+  if (!use_legacy_attn() && packed && Lk <= 1024 && Lq <= 1024)
     return attn_bwd_tc(q, ldq, k, ldkv, mask, kv_end, dctx, ldc, lse, delta, reinterpret_cast<float*>(workspace), dq,
                        lddq, dk, dv, lddkv, B, H, Lq, Lk, s);
   static bool attr = false;

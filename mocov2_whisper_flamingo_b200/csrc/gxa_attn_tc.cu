@@ -9,6 +9,8 @@
 //             P_j written as bf16 into a 128B-swizzled K-major smem tile (the A operand of the PV MMA),
 //             running output kept in registers: O = (O + O_{j-1}) * alpha_j.
 // 96 KB smem and 256 TMEM columns per CTA -> two CTAs per SM overlap each other's softmax and MMA phases.
+#include <cstdlib>
+
 #include "gxa_host.h"
 #include "gxa_ptx.cuh"
 
@@ -320,7 +322,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                    const __grid_constant__ CUtensorMap tmDO, const uint8_t* __restrict__ mask,
                    const int* __restrict__ kv_end, const float* __restrict__ lse, const float* __restrict__ delta,
                    float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dk, __nv_bfloat16* __restrict__ dv, int lddkv,
-                   int H, int Lq, int Lk, int D, int LqPad) {
+                   int H, int Lq, int Lk, int D, int LqPad, int dbg) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   BwdTcSmem& sm = *reinterpret_cast<BwdTcSmem*>(smem_raw);
   if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
@@ -548,7 +550,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync 2, 128;" ::: "memory");
-      if (issuer) {
+      if (issuer && !(dbg & 1)) {
         bulk_reduce_add_f32(gbase + size_t(i) * TC_BQ * TC_HD, sm.dq_stage, TC_BQ * TC_HD * 4);
         bulk_commit_group();
       }
@@ -564,7 +566,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 }
 
 // dq(bf16)[b, q, h*64 + d] = 0.125 * acc[b, h, q, d]
-__global__ void __launch_bounds__(256)
+__global__ void
 attn_dq_finalize_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int lddq, int H, int Lq,
                         int LqPad, size_t total4) {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total4; i += size_t(gridDim.x) * blockDim.x) {
@@ -607,7 +609,8 @@ int attn_bwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t*
   dim3 grid((Lk + TC_BK - 1) / TC_BK, H, B);
   attn_bwd_tc_kernel<<<grid, TCB_THREADS, BWD_TC_SMEM, s>>>(tmQ, tmKV, tmDO, mask, kv_end, lse, delta, dq_acc,
                                                            reinterpret_cast<__nv_bfloat16*>(dk),
-                                                           reinterpret_cast<__nv_bfloat16*>(dv), lddkv, H, Lq, Lk, D, LqPad);
+                                                           reinterpret_cast<__nv_bfloat16*>(dv), lddkv, H, Lq, Lk, D, LqPad,
+                                                           getenv("GXA_DBG") ? atoi(getenv("GXA_DBG")) : 0);
   count_launch();
   if (cudaGetLastError() != cudaSuccess) return GXA_ERR_CUDA;
   const size_t total4 = size_t(B) * H * Lq * 16;

@@ -50,13 +50,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a pipeline bug must trap (the launch then reports an error) instead of
-// hanging the GPU box.  ~4 s at 2 GHz.
+// Bounded wait: a pipeline bug must trap (the launch then reports an error) instead of hanging the GPU box.
+// The poll loop is kept to try_wait + counter + branch: waiting warps share their scheduler with the math warps,
+// and the earlier clock64-based timeout cost 9 issue slots per poll (ncu: a quarter of all executed instructions).
+// try_wait itself suspends the warp for a hardware time slice, so 2^26 polls is several seconds.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  long long t0 = clock64();
+  uint32_t polls = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 8000000000LL) {
+    if (++polls == (1u << 26)) {
       printf("gxa: mbarrier wait timed out (block %d thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
       __trap();
     }
@@ -237,4 +239,49 @@ __device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, const void* sme
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+}  // namespace gxa
+
+// ---------------------------------------------------------------- converged single-thread issue
+// The MMA warp stays CONVERGED: every lane computes the (warp-uniform) descriptors, so they live in uniform registers,
+// and only the tcgen05 instruction itself is predicated on the elected lane.  Issuing from inside `if (lane == 0)`
+// makes the compiler wrap every tcgen05.mma in an elect/vote loop (~16 SASS instructions per MMA), which is what
+// limits the MMA issue rate when busy math warps share the issuing warp's scheduler.
+namespace gxa {
+__device__ __forceinline__ uint32_t elect_one_pred() {   // 1 in exactly one lane of the (converged) warp
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}\n"
+      : "=r"(pred));
+  return pred;
+}
+// low word of a 128B-swizzle descriptor: start address and leading byte offset; add (bytes >> 4) to advance
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+// high word: stride byte offset, version 1, layout type 2 (128B swizzle)
+__host__ __device__ constexpr uint32_t umma_desc_hi(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+}
+__device__ __forceinline__ void umma_bf16_e(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                            uint32_t idesc, uint32_t accumulate, uint32_t elected) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.ne.b32 e, %7, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n"
+      ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(elected)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_e(uint64_t* bar, uint32_t elected) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "setp.ne.b32 e, %1, 0;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n"
+      ::"r"(smem_u32(bar)), "r"(elected)
+      : "memory");
+}
 }  // namespace gxa
