@@ -16,7 +16,7 @@ namespace gxa {
 
 constexpr int G2_BM = 256;        // per pair
 constexpr int G2_BN = 256;
-constexpr int G2_STAGES = 5;
+constexpr int G2_STAGES = 6;
 constexpr int G2_A_BYTES = 128 * GEMM_BK * 2;      // this CTA's 128 rows of A
 constexpr int G2_B_BYTES = 128 * GEMM_BK * 2;      // this CTA's 128 columns of B
 constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_B_BYTES;
@@ -108,6 +108,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ------------------------------------------------------------ MMA issuer (leader CTA only)
     if (leader) {
       constexpr uint32_t idesc = umma_idesc_bf16(G2_BM, G2_BN, A_MN, B_MN);
+      // converged issue (gxa_ptx.cuh): descriptors are warp-uniform values computed by all lanes; only the tcgen05
+      // instructions are predicated on the elected lane
+      constexpr uint32_t HI = umma_desc_hi(1024);
+      constexpr uint32_t A_LBO = A_MN ? 8192 : 16, B_LBO = B_MN ? 8192 : 16;
+      constexpr uint32_t A_STEP = (A_MN ? 2048 : 32) >> 4, B_STEP = (B_MN ? 2048 : 32) >> 4;
+      const uint32_t el = elect_one_pred();
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -122,24 +128,16 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t a_base = smem_u32(smem + stage * G2_STAGE_BYTES);
-            const uint32_t b_base = a_base + G2_A_BYTES;
+          const uint32_t a_base = smem_u32(smem + stage * G2_STAGE_BYTES);
+          const uint32_t da = umma_desc_lo(a_base, A_LBO), db = umma_desc_lo(a_base + G2_A_BYTES, B_LBO);
+          const uint32_t acc0 = kb > kb0 ? 1u : 0u;
 #pragma unroll
-            for (int k = 0; k < GEMM_BK / 16; ++k) {
-              const uint64_t da = A_MN ? umma_desc_sw128(a_base + k * 2048, 8192, 1024)
-                                       : umma_desc_sw128(a_base + k * 32, 16, 1024);
-              const uint64_t db = B_MN ? umma_desc_sw128(b_base + k * 2048, 8192, 1024)
-                                       : umma_desc_sw128(b_base + k * 32, 16, 1024);
-              umma_bf16_pair(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            }
-            umma_commit_pair(&empty[stage], 3);     // frees this smem slot in BOTH CTAs
-          }
-          __syncwarp();
+          for (int k = 0; k < GEMM_BK / 16; ++k)
+            umma_bf16_pair_e(tmem_d, da + k * A_STEP, HI, db + k * B_STEP, HI, idesc, k > 0 ? 1u : acc0, el);
+          umma_commit_pair_e(&empty[stage], 3, el);     // frees this smem slot in BOTH CTAs
           if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
         }
-        if (lane == 0) umma_commit_pair(&tfull[as], 3);   // accumulator ready in both CTAs
-        __syncwarp();
+        umma_commit_pair_e(&tfull[as], 3, el);          // accumulator ready in both CTAs
         as ^= 1;
         if (as == 0) aphase ^= 1;
       }
