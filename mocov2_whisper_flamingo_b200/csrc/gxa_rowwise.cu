@@ -193,6 +193,141 @@ ln_bwd_kernel(const void* __restrict__ g, int g_is_f32, const float* __restrict_
   }
 }
 
+// ------------------------------------------------------------------ LayerNorm backward, row split over W warps
+// One row is owned by W warps of a block (NVW float4 per lane): the per-lane state (row values + three sets of
+// per-column partial sums) shrinks W-fold, so several blocks stay resident per SM, and the loads of BOTH phases
+// (g, x and the residual gradient / gate operand) are issued before the row reduction -- enough bytes in flight to
+// reach HBM bandwidth.  (The one-warp-per-row kernel above needs 252 registers at D = 1024: 8 warps per SM.)
+template <int NVW, int W, bool GATED>
+__global__ void __launch_bounds__(RW_WARPS * 32)
+ln_bwd_split_kernel(const void* __restrict__ g, int g_is_f32, const float* __restrict__ x, const float* __restrict__ w,
+                    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ dres,
+                    float* __restrict__ dx, float* __restrict__ dw, float* __restrict__ db, const void* __restrict__ o,
+                    int o_is_f32, const float* __restrict__ gate, float* __restrict__ dgate_accum, void* __restrict__ dout,
+                    float* __restrict__ dbias_out, int rows) {
+  constexpr int D = 128 * NVW * W;
+  constexpr int GROUPS = RW_WARPS / W;
+  extern __shared__ float sm[];                       // [GROUPS][D] column flush
+  __shared__ float red[2][GROUPS][W][2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rg = warp / W, wq = warp % W;
+  float4 aw[NVW], ab[NVW], ao[NVW];
+#pragma unroll
+  for (int i = 0; i < NVW; ++i) aw[i] = ab[i] = ao[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float gate_t = 0.f, gacc = 0.f;
+  if (GATED) gate_t = tanhf(__ldg(gate));
+  int par = 0;
+  for (int row = blockIdx.x * GROUPS + rg; row < rows; row += gridDim.x * GROUPS, par ^= 1) {
+    const size_t base = size_t(row) * D;
+    const float mu = __ldg(mean + row), rs = __ldg(rstd + row);
+    float4 gv[NVW], xh[NVW], rv[NVW], ov[NVW];
+#pragma unroll
+    for (int i = 0; i < NVW; ++i) {                   // every load of the row first
+      const int c = (i * W + wq) * 128 + lane * 4;
+      gv[i] = ld4_any(g, base + c, g_is_f32);
+      xh[i] = ld4(x + base + c);
+      rv[i] = dres ? ld4(dres + base + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (GATED) ov[i] = ld4_any(o, base + c, o_is_f32);
+    }
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NVW; ++i) {
+      const int c = (i * W + wq) * 128 + lane * 4;
+      const float4 wv = __ldg(reinterpret_cast<const float4*>(w + c));
+      xh[i] = make_float4((xh[i].x - mu) * rs, (xh[i].y - mu) * rs, (xh[i].z - mu) * rs, (xh[i].w - mu) * rs);
+      aw[i].x += gv[i].x * xh[i].x; aw[i].y += gv[i].y * xh[i].y; aw[i].z += gv[i].z * xh[i].z; aw[i].w += gv[i].w * xh[i].w;
+      ab[i].x += gv[i].x; ab[i].y += gv[i].y; ab[i].z += gv[i].z; ab[i].w += gv[i].w;
+      gv[i].x *= wv.x; gv[i].y *= wv.y; gv[i].z *= wv.z; gv[i].w *= wv.w;
+      s1 += gv[i].x + gv[i].y + gv[i].z + gv[i].w;
+      s2 += gv[i].x * xh[i].x + gv[i].y * xh[i].y + gv[i].z * xh[i].z + gv[i].w * xh[i].w;
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) { red[par][rg][wq][0] = s1; red[par][rg][wq][1] = s2; }
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + rg), "n"(W * 32) : "memory");
+    s1 = 0.f; s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < W; ++k) { s1 += red[par][rg][k][0]; s2 += red[par][rg][k][1]; }
+    s1 *= (1.0f / D);
+    s2 *= (1.0f / D);
+#pragma unroll
+    for (int i = 0; i < NVW; ++i) {
+      const int c = (i * W + wq) * 128 + lane * 4;
+      float4 d;
+      d.x = rv[i].x + rs * (gv[i].x - s1 - xh[i].x * s2);
+      d.y = rv[i].y + rs * (gv[i].y - s1 - xh[i].y * s2);
+      d.z = rv[i].z + rs * (gv[i].z - s1 - xh[i].z * s2);
+      d.w = rv[i].w + rs * (gv[i].w - s1 - xh[i].w * s2);
+      *reinterpret_cast<float4*>(dx + base + c) = d;
+      if (GATED) {
+        gacc += d.x * ov[i].x + d.y * ov[i].y + d.z * ov[i].z + d.w * ov[i].w;
+        float4 t = make_float4(gate_t * d.x, gate_t * d.y, gate_t * d.z, gate_t * d.w);
+        if (!o_is_f32) {   // bf16 path: the bias gradient sums what the dgrad GEMM will see
+          t.x = __bfloat162float(__float2bfloat16_rn(t.x)); t.y = __bfloat162float(__float2bfloat16_rn(t.y));
+          t.z = __bfloat162float(__float2bfloat16_rn(t.z)); t.w = __bfloat162float(__float2bfloat16_rn(t.w));
+        }
+        st4_any(dout, base + c, o_is_f32, t);
+        ao[i].x += t.x; ao[i].y += t.y; ao[i].z += t.z; ao[i].w += t.w;
+      }
+    }
+  }
+  // flush the per-column partials: one atomicAdd per column per block
+  auto flush = [&](float4 (&acc)[NVW], float* __restrict__ dst) {
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NVW; ++i) *reinterpret_cast<float4*>(sm + rg * D + (i * W + wq) * 128 + lane * 4) = acc[i];
+    __syncthreads();
+    for (int c = threadIdx.x; c < D; c += RW_WARPS * 32) {
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < GROUPS; ++k) t += sm[k * D + c];
+      atomicAdd(dst + c, t);
+    }
+  };
+  flush(aw, dw);
+  flush(ab, db);
+  if (GATED) {
+    flush(ao, dbias_out);
+    gacc = warp_sum(gacc);
+    if (lane == 0) atomicAdd(dgate_accum, gacc);
+  }
+}
+
+// persistent grid = what is actually resident (a partial second wave of equal-sized blocks would double the time)
+template <typename K>
+static int resident_grid(K kern, size_t smem, int rows, int rows_per_block) {
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, RW_WARPS * 32, smem) != cudaSuccess || nb < 1) nb = 1;
+  const int blocks = (rows + rows_per_block - 1) / rows_per_block;
+  const int cap = num_sms() * nb;
+  return blocks < cap ? blocks : cap;
+}
+
+template <int NVW, int W>
+static int ln_bwd_split_launch(const void* g, int g_is_f32, const float* x, const float* w, const float* mean,
+                               const float* rstd, const float* dres, float* dx, float* dw, float* db, const void* o,
+                               int o_is_f32, const float* gate, float* dgate_accum, void* dout, float* dbias_out, int rows,
+                               cudaStream_t s) {
+  constexpr int D = 128 * NVW * W, GROUPS = RW_WARPS / W;
+  const size_t smem = sizeof(float) * GROUPS * D;
+  if (o != nullptr) {
+    auto k = ln_bwd_split_kernel<NVW, W, true>;
+    static int grid_cap = 0;
+    if (!grid_cap) grid_cap = resident_grid(k, smem, 1 << 30, GROUPS);
+    const int blocks = (rows + GROUPS - 1) / GROUPS;
+    k<<<blocks < grid_cap ? blocks : grid_cap, RW_WARPS * 32, smem, s>>>(g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, o,
+                                                                          o_is_f32, gate, dgate_accum, dout, dbias_out, rows);
+  } else {
+    auto k = ln_bwd_split_kernel<NVW, W, false>;
+    static int grid_cap = 0;
+    if (!grid_cap) grid_cap = resident_grid(k, smem, 1 << 30, GROUPS);
+    const int blocks = (rows + GROUPS - 1) / GROUPS;
+    k<<<blocks < grid_cap ? blocks : grid_cap, RW_WARPS * 32, smem, s>>>(g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db,
+                                                                          nullptr, 0, nullptr, nullptr, nullptr, nullptr, rows);
+  }
+  return check_launch();
+}
+
 static inline int rowwise_grid(int rows) {
   int blocks = (rows + RW_WARPS - 1) / RW_WARPS;
   int cap = num_sms() * 4;
@@ -204,6 +339,18 @@ int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const fl
            float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s) {
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
+#define GXA_LN_SPLIT(NVW, W) \
+  return ln_bwd_split_launch<NVW, W>(g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, o, o_is_f32, gate, dgate_accum, dout, \
+                                     dbias_out, rows, s)
+  switch (D / 128) {
+    case 8: GXA_LN_SPLIT(2, 4);
+    case 4: GXA_LN_SPLIT(1, 4);
+    case 6: GXA_LN_SPLIT(3, 2);
+    case 10: GXA_LN_SPLIT(5, 2);
+    case 2: GXA_LN_SPLIT(1, 2);
+    default: break;
+  }
+#undef GXA_LN_SPLIT
   const int grid = rowwise_grid(rows);
   const size_t smem = sizeof(float) * RW_WARPS * D;
   if (o != nullptr) {
@@ -259,8 +406,9 @@ int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, fl
              int out_is_f32, float* dbias, int rows, int D, cudaStream_t s) {
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
-  const int grid = rowwise_grid(rows);
   const size_t smem = sizeof(float) * RW_WARPS * D;
+  int grid = 1;
+  GXA_NV_DISPATCH(D, (grid = resident_grid(gate_bwd_kernel<NV>, smem, rows, RW_WARPS)));
   GXA_NV_DISPATCH(D, (gate_bwd_kernel<NV><<<grid, RW_WARPS * 32, smem, s>>>(dy, f, f_is_f32, gate, dgate_accum, dout,
                                                                             out_is_f32, dbias, rows)));
   return check_launch();
