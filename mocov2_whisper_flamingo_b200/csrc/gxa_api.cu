@@ -147,8 +147,9 @@ static int gemm_f32(const float* A, int lda, bool a_mn, const float* B, int ldb,
 
 static int gemm_bf16(const void* A, int lda, bool a_mn, const void* B, int ldb, bool b_mn, int M, int N, int K, int epi,
                      void* C, int ldc, void* C2, int ldc2, const float* bias, const void* aux, int ld_aux,
-                     const float* gate, int accumulate, cudaStream_t s) {
+                     const float* gate, int accumulate, cudaStream_t s, float* colsum_out = nullptr) {
   GemmOp op;
+  op.colsum = colsum_out;
   op.A = A; op.lda = lda; op.a_mn = a_mn; op.B = B; op.ldb = ldb; op.b_mn = b_mn;
   op.M = M; op.N = N; op.K = K; op.epi = epi; op.C = C; op.ldc = ldc; op.C2 = C2; op.ldc2 = ldc2;
   op.bias = bias; op.aux = aux; op.ld_aux = ld_aux; op.gate = gate; op.accumulate = accumulate;
@@ -231,10 +232,9 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   // ---- FFN branch
   GXA_TRY(gate_bwd(dy, S.f, 0, p.ff_gate, Wk.gacc + 1, Wk.df, 0, g.ff2_b, M, D, s));
   GXA_TRY(gemm_bf16(Wk.df, D, false, W.ff2, 4 * D, true, M, 4 * D, D, EPI_GELU_BWD, Wk.du, 4 * D, nullptr, 0, nullptr,
-                    S.u, 4 * D, nullptr, 0, s));
+                    S.u, 4 * D, nullptr, 0, s, g.ff0_b));     // d(ff.0.bias) = colsum(du) fused in the epilogue
   GXA_TRY(gemm_bf16(Wk.df, D, true, S.a, 4 * D, true, D, 4 * D, M, EPI_F32, g.ff2_w, 4 * D, nullptr, 0, nullptr, nullptr,
                     0, nullptr, 1, s));
-  GXA_TRY(colsum(Wk.du, 0, 4 * D, g.ff0_b, M, 4 * D, s));
   GXA_TRY(gemm_bf16(Wk.du, 4 * D, false, W.ff0, D, true, M, D, 4 * D, EPI_BF16, Wk.dh2, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 0, s));
   GXA_TRY(gemm_bf16(Wk.du, 4 * D, true, S.h2, D, true, 4 * D, D, M, EPI_F32, g.ff0_w, D, nullptr, 0, nullptr, nullptr, 0,
@@ -255,8 +255,7 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
                     nullptr, 1, s));
   // ---- attention core
   GXA_TRY(attn_bwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, Wk.dctx, D, S.lse, Wk.delta, Wk.dq, D,
-                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s));
-  GXA_TRY(colsum(Wk.dq, 0, D, g.in_proj_b, M, D, s));
+                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s, g.in_proj_b));   // + fused d(bq)
   GXA_TRY(colsum(Wk.dkv, 0, 2 * D, g.in_proj_b + D, Mk, 2 * D, s));
   GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 1, s));

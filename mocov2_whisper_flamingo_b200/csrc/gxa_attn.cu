@@ -446,14 +446,15 @@ int attn_bwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t*
                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
 int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
                  const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
-                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
+                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s);
 size_t attn_bwd_tc_workspace(int B, int H, int Lq);
 
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_tc_workspace(B, H, Lq); }
 
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
-                  void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s) {
+                  void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s,
+                  float* dq_colsum) {
   if (B <= 0 || H <= 0 || Lq <= 0 || Lk <= 0) return GXA_ERR_SHAPE;
   if ((ldq % 8) || (ldkv % 8) || (ldc % 8) || (lddq % 8) || (lddkv % 8)) return GXA_ERR_ALIGN;
   auto Q = reinterpret_cast<const __nv_bfloat16*>(q);
@@ -469,7 +470,12 @@ int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
   static const bool bwd_v1 = getenv("GXA_ATTN_BWD") && getenv("GXA_ATTN_BWD")[0] == '1';   // A/B: per-item CTAs
   if (!use_legacy_attn() && packed && !bwd_v1)       // persistent tcgen05 kernel (any Lq, Lk)
     return attn_bwd_tc2(q, ldq, k, ldkv, mask, kv_end, dctx, ldc, lse, delta, reinterpret_cast<float*>(workspace), dq,
-                        lddq, dk, dv, lddkv, B, H, Lq, Lk, s);
+                        lddq, dk, dv, lddkv, B, H, Lq, Lk, dq_colsum, s);
+  if (dq_colsum != nullptr) {     // the other paths have no fused d(bq): one pass over dq afterwards
+    const int e = attn_bwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, dctx, ldc, lse, delta, dq, lddq, dk, dv, lddkv,
+                                workspace, B, H, Lq, Lk, s, nullptr);
+    return e ? e : colsum(dq, 0, lddq, dq_colsum, B * Lq, H * 64, s);
+  }
   if (!use_legacy_attn() && packed && Lk <= 1024 && Lq <= 1024)
     return attn_bwd_tc(q, ldq, k, ldkv, mask, kv_end, dctx, ldc, lse, delta, reinterpret_cast<float*>(workspace), dq,
                        lddq, dk, dv, lddkv, B, H, Lq, Lk, s);

@@ -462,7 +462,8 @@ namespace gxa {
 // dq(bf16)[b, q, h*64 + d] = 0.125 * acc[b, h, q-block, d/4, q%128, d%4]   (one block per 128-query tile; the
 // transposition between the reduction-friendly accumulator layout and row-major dq goes through shared memory)
 __global__ void __launch_bounds__(256)
-attn_dq_finalize2_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int lddq, int H, int Lq, int nq) {
+attn_dq_finalize2_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int lddq, int H, int Lq, int nq,
+                         float* __restrict__ dq_colsum) {
   __shared__ float4 tile[16][BQ + 1];
   const int blk = blockIdx.x;                       // (b*H + h)*nq + i
   const int i = blk % nq, bh = blk / nq, h = bh % H, b = bh / H;
@@ -486,6 +487,13 @@ attn_dq_finalize2_kernel(const float* __restrict__ acc, __nv_bfloat16* __restric
       *reinterpret_cast<uint2*>(dq + (size_t(b) * Lq + qrow) * lddq + h * HD + jj * 4) = o;
     }
   }
+  if (dq_colsum != nullptr) {      // fused d(bq): column sums of the bf16 dq rows this tile wrote
+    const int c = threadIdx.x & 63, r0 = (threadIdx.x >> 6) * 32;
+    float sum = 0.f;
+    for (int row = r0; row < r0 + 32 && i * BQ + row < Lq; ++row)
+      sum += __bfloat162float(__float2bfloat16_rn(reinterpret_cast<const float*>(&tile[c >> 2][row])[c & 3] * 0.125f));
+    atomicAdd(dq_colsum + h * HD + c, sum);
+  }
 }
 
 size_t attn_bwd_tc_workspace(int B, int H, int Lq);
@@ -493,7 +501,7 @@ size_t attn_bwd_tc_workspace(int B, int H, int Lq);
 // Persistent backward (see the header of this file).  Same contract as attn_bwd_tc.
 int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
                  const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
-                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s) {
+                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s) {
   const int D = H * HD;
   const int LqPad = (Lq + BQ - 1) / BQ * BQ;
   CUtensorMap tmQ, tmKV, tmDO;
@@ -517,7 +525,7 @@ int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t
   count_launch();
   if (cudaGetLastError() != cudaSuccess) return GXA_ERR_CUDA;
   attn_dq_finalize2_kernel<<<B * H * (LqPad / BQ), 256, 0, s>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), lddq, H, Lq,
-                                                               LqPad / BQ);
+                                                               LqPad / BQ, dq_colsum);
   count_launch();
   return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }

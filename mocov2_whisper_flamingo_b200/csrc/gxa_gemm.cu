@@ -274,7 +274,7 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
   GemmParams p;
   p.M = op.M; p.N = op.N; p.K = op.K;
   p.C = op.C; p.ldc = op.ldc; p.C2 = op.C2; p.ldc2 = op.ldc2;
-  p.bias = op.bias; p.aux = op.aux; p.ld_aux = op.ld_aux; p.gate = op.gate; p.accumulate = op.accumulate;
+  p.bias = op.bias; p.aux = op.aux; p.ld_aux = op.ld_aux; p.gate = op.gate; p.accumulate = op.accumulate; p.colsum = op.colsum;
   const int kb_total = (op.K + GEMM_BK - 1) / GEMM_BK;
   int bn = op.bn;
   if (bn == 0) {
@@ -307,10 +307,14 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
         return GXA_ERR_CUDA;
     }
   }
+  if (op.colsum != nullptr && op.epi != EPI_GELU_BWD) return GXA_ERR_UNSUPPORTED;
   if (pair) return gemm2_launch(op, p, stream);
-  if (bn == 256) return launch_epi<256>(op, p, stream);
-  if (bn == 128) return launch_epi<128>(op, p, stream);
-  return GXA_ERR_UNSUPPORTED;
+  int e = GXA_ERR_UNSUPPORTED;
+  if (bn == 256) e = launch_epi<256>(op, p, stream);
+  else if (bn == 128) e = launch_epi<128>(op, p, stream);
+  // the small-problem kernel has no fused column sum: one extra pass over its (bf16) output
+  if (e == 0 && op.colsum != nullptr) e = colsum(op.C, 0, op.ldc, op.colsum, op.M, op.N, stream);
+  return e;
 }
 
 }  // namespace gxa

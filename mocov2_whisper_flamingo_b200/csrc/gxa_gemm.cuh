@@ -37,6 +37,7 @@ struct GemmParams {
   int ld_aux;
   const float* gate;   // device scalar, tanh applied in-kernel
   int accumulate;
+  float* colsum;       // EPI_GELU_BWD: colsum[n] += sum over rows of the (bf16-rounded) output, i.e. the bias gradient
 };
 
 constexpr int GEMM_BM = 128;
@@ -255,6 +256,7 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
   const int c = col + 4 * cl;
   float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
   if (p.bias != nullptr && first_split) b = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+  float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int it = 0; it < 8; ++it) {
     const int rr = it * 4 + rsub;
@@ -290,8 +292,20 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
       a = round_bf16x4(a);
       const float4 u = unpack_bf16x4(ax.v[it]);
       const float2 g0 = gelu_grad_fast2(make_float2(u.x, u.y)), g1 = gelu_grad_fast2(make_float2(u.z, u.w));
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) =
-          pack_bf16x4(make_float4(a.x * g0.x, a.y * g0.y, a.z * g1.x, a.w * g1.y));
+      const uint2 pk = pack_bf16x4(make_float4(a.x * g0.x, a.y * g0.y, a.z * g1.x, a.w * g1.y));
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pk;
+      const float4 orr = unpack_bf16x4(pk);
+      cs.x += orr.x; cs.y += orr.y; cs.z += orr.z; cs.w += orr.w;
+    }
+  }
+  if constexpr (EPI == EPI_GELU_BWD) {
+    if (p.colsum != nullptr) {      // 32 rows of this chunk -> one vector reduction per 4 columns
+#pragma unroll
+      for (int o = 8; o <= 16; o <<= 1) {
+        cs.x += __shfl_xor_sync(0xffffffffu, cs.x, o); cs.y += __shfl_xor_sync(0xffffffffu, cs.y, o);
+        cs.z += __shfl_xor_sync(0xffffffffu, cs.z, o); cs.w += __shfl_xor_sync(0xffffffffu, cs.w, o);
+      }
+      if (rsub == 0) atomicAdd(reinterpret_cast<float4*>(p.colsum + c), cs);
     }
   }
   __syncwarp();

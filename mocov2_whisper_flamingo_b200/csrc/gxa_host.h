@@ -29,6 +29,7 @@ struct GemmOp {
   const void* aux = nullptr; int ld_aux = 0;
   const float* gate = nullptr;
   int accumulate = 0;
+  float* colsum = nullptr;   // EPI_GELU_BWD only: += column sums of the output (fused bias gradient)
   int bn = 0;        // 0 = choose
   int k_splits = 0;  // 0 = choose
 };
@@ -67,7 +68,8 @@ int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
                   void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s);
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
-                  void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s);
+                  void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s,
+                  float* dq_colsum = nullptr);   // optional: += column sums of dq (fused bias gradient)
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq);
 int attn_fwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const uint8_t* mask, float* ctx,
                  int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s);

@@ -1,0 +1,51 @@
+// Counter-based dropout bits shared by every kernel that applies or re-creates a dropout mask
+// (reference: nn.MultiheadAttention(dropout=p) -> dropout on the attention probabilities inside SDPA, and
+// nn.Dropout(p) after ff.2 -- models/gate_cross_attention.py:16, :26).  Nothing is stored: forward and backward
+// evaluate the same function of (seed, element), so the mask costs no HBM traffic.
+//
+//   keep(row, col) = u16(row, col) >= thresh,   thresh = round(p * 65536)   (drop probability thresh / 65536)
+//   u16(row, col)  = 16-bit half (col & 1) of mix(seed, row * ceil(ncols / 2) + (col >> 1))
+//
+// One 32-bit mix yields the decision for two neighbouring columns; the counter wraps modulo 2^32.
+// tests/dropout_ref.py holds the numpy restatement used by the parity tests.
+#pragma once
+#include <stdint.h>
+
+namespace gxa {
+
+struct DropCfg {
+  uint32_t thresh;     // 0 = dropout off
+  float scale;         // 1 / (1 - p)
+  uint32_t seed_lo, seed_hi;
+};
+
+__host__ __device__ __forceinline__ uint32_t drop_mix(uint32_t ctr, uint32_t seed_lo, uint32_t seed_hi) {
+  uint32_t x = ctr ^ seed_lo;
+  x ^= x >> 16; x *= 0x7feb352dU;
+  x ^= x >> 15; x *= 0x846ca68bU;
+  x ^= x >> 16;
+  x = (x ^ seed_hi) * 0x9E3779B1U;
+  x ^= x >> 15;
+  return x;
+}
+// scale factors (0 or cfg.scale) for the column pair (2*pair, 2*pair + 1) of a row whose pair counter starts at row_ctr
+__device__ __forceinline__ void drop_pair(const DropCfg& c, uint32_t ctr, float& m0, float& m1) {
+  const uint32_t x = drop_mix(ctr, c.seed_lo, c.seed_hi);
+  m0 = (x & 0xffffu) >= c.thresh ? c.scale : 0.f;
+  m1 = (x >> 16) >= c.thresh ? c.scale : 0.f;
+}
+inline DropCfg make_drop_cfg(float p, uint64_t seed, uint32_t stream) {
+  DropCfg c;
+  c.thresh = 0; c.scale = 1.f; c.seed_lo = 0; c.seed_hi = 0;
+  if (p > 0.f) {
+    double t = double(p) * 65536.0 + 0.5;
+    c.thresh = t >= 65535.0 ? 65535u : uint32_t(t);
+    c.scale = 1.0f / (1.0f - p);
+    c.seed_lo = uint32_t(seed) ^ (stream * 0x85ebca6bU);
+    c.seed_hi = uint32_t(seed >> 32) + stream * 0xc2b2ae35U;
+  }
+  return c;
+}
+constexpr uint32_t kDropStreamAttn = 1, kDropStreamFfn = 2;
+
+}  // namespace gxa
