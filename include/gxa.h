@@ -40,6 +40,13 @@ typedef struct gxa_dims {
                           torch.autocast(bf16)); GXA_PREC_FP32: 3xbf16 split contractions, fp32 everywhere */
   int32_t has_xa;      /* 0 => FFN only (reference forward with xa=None, :39) */
   int32_t reserved;
+  /* training-mode dropout (models/gate_cross_attention.py:16 nn.MultiheadAttention(dropout=p) -> on the attention
+   * probabilities; :26 nn.Dropout(p) after ff.2).  p_drop = 0 disables it (eval mode).  The masks are a pure
+   * function of (seed, element) -- csrc/gxa_rng.cuh -- so forward and backward must be called with the same seed;
+   * give every (step, layer) its own seed.  bf16 precision only. */
+  float p_drop;
+  uint32_t reserved2;
+  uint64_t seed;
 } gxa_dims;
 
 /* The 14 state_dict tensors of one block, fp32, in the reference's layout. */
@@ -95,7 +102,7 @@ int gxa_mask_prepare(const uint8_t* mask, int32_t* kv_end, int B, int Lk, void* 
 size_t gxa_xa_operand_bytes(const gxa_dims* d);
 int gxa_xa_prepare(const gxa_dims* d, const float* xa, void* xa_op, void* stream);
 
-/* GatedCrossAttentionBlock.forward (models/gate_cross_attention.py:28-50), dropout = 0.
+/* GatedCrossAttentionBlock.forward (models/gate_cross_attention.py:28-50); dropout per d->p_drop / d->seed.
  * x, y: fp32 [B*Lq, D] contiguous; xa_op from gxa_xa_prepare; mask/kv_end from gxa_mask_prepare
  * (mask may be NULL = no padding).  `saved` receives what backward needs (pass NULL for
  * inference).  y may not alias x. */
@@ -138,11 +145,19 @@ int gxa_attn_fwd(const void* q, int ldq, const void* k, const void* v, int ldkv,
                  const int32_t* kv_end, void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, void* stream);
 /* workspace: gxa_attn_bwd_workspace_bytes() of scratch (fp32 dQ accumulator of the tcgen05 path); NULL selects the
  * scratch-free legacy kernels. */
+/* the same with dropout on the attention probabilities (p_drop in [0,1), mask = f(seed, b, h, q, key)) */
+int gxa_attn_fwd_dropout(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
+                         const int32_t* kv_end, void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk,
+                         float p_drop, uint64_t seed, void* stream);
 size_t gxa_attn_bwd_workspace_bytes(int B, int H, int Lq);
 int gxa_attn_bwd(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
                  const int32_t* kv_end, const void* ctx, const void* dctx, int ldc, const float* lse, float* delta,
                  void* dq, int lddq, void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk,
                  void* stream);
+int gxa_attn_bwd_dropout(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
+                         const int32_t* kv_end, const void* ctx, const void* dctx, int ldc, const float* lse,
+                         float* delta, void* dq, int lddq, void* dk, void* dv, int lddkv, void* workspace, int B, int H,
+                         int Lq, int Lk, float p_drop, uint64_t seed, void* stream);
 
 #ifdef __cplusplus
 }

@@ -21,8 +21,9 @@ PARAM_FIELDS = ("attn_gate", "ff_gate", "in_proj_w", "in_proj_b", "out_proj_w", 
                 "attn_ln_b", "ff_ln_w", "ff_ln_b", "ff0_w", "ff0_b", "ff2_w", "ff2_b")
 
 
-class Dims(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("B", "Lq", "Lk", "D", "H", "precision", "has_xa", "reserved")]
+class Dims(C.Structure):      # gxa_dims
+    _fields_ = [(n, C.c_int32) for n in ("B", "Lq", "Lk", "D", "H", "precision", "has_xa", "reserved")] + \
+               [("p_drop", C.c_float), ("reserved2", C.c_uint32), ("seed", C.c_uint64)]
 
 
 class BlockPtrs(C.Structure):   # gxa_block_params and gxa_block_grads share this shape
@@ -55,9 +56,13 @@ SIGNATURES = {
     "gxa_gemm_bf16": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i,
                            _vp]),
     "gxa_attn_fwd": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp]),
+    "gxa_attn_fwd_dropout": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, C.c_float, C.c_uint64,
+                                  _vp]),
     "gxa_attn_bwd_workspace_bytes": (_sz, [_i, _i, _i]),
     "gxa_attn_bwd": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i,
                           _i, _vp]),
+    "gxa_attn_bwd_dropout": (_i, [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i,
+                                  _i, _i, _i, C.c_float, C.c_uint64, _vp]),
 }
 
 _lib = None

@@ -126,6 +126,8 @@ static int check_dims(const gxa_dims* d) {
   if (d->has_xa && d->Lk <= 0) return GXA_ERR_SHAPE;
   if (d->D != d->H * 64 || d->D % 128 != 0) return GXA_ERR_SHAPE;
   if (d->precision != GXA_PREC_BF16 && d->precision != GXA_PREC_FP32) return GXA_ERR_UNSUPPORTED;
+  if (!(d->p_drop >= 0.f && d->p_drop < 1.f)) return GXA_ERR_ARG;
+  if (d->p_drop > 0.f && d->precision != GXA_PREC_BF16) return GXA_ERR_UNSUPPORTED;   // dropout: bf16 training mode only
   return 0;
 }
 
@@ -147,9 +149,11 @@ static int gemm_f32(const float* A, int lda, bool a_mn, const float* B, int ldb,
 
 static int gemm_bf16(const void* A, int lda, bool a_mn, const void* B, int ldb, bool b_mn, int M, int N, int K, int epi,
                      void* C, int ldc, void* C2, int ldc2, const float* bias, const void* aux, int ld_aux,
-                     const float* gate, int accumulate, cudaStream_t s, float* colsum_out = nullptr) {
+                     const float* gate, int accumulate, cudaStream_t s, float* colsum_out = nullptr,
+                     DropCfg drop = DropCfg{0, 1.f, 0, 0}) {
   GemmOp op;
   op.colsum = colsum_out;
+  op.drop = drop;
   op.A = A; op.lda = lda; op.a_mn = a_mn; op.B = B; op.ldb = ldb; op.b_mn = b_mn;
   op.M = M; op.N = N; op.K = K; op.epi = epi; op.C = C; op.ldc = ldc; op.C2 = C2; op.ldc2 = ldc2;
   op.bias = bias; op.aux = aux; op.ld_aux = ld_aux; op.gate = gate; op.accumulate = accumulate;
@@ -180,7 +184,8 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
                       nullptr, 0, s));
     GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, S.kv, 2 * D, nullptr,
                       0, p.in_proj_b + D, nullptr, 0, nullptr, 0, s));
-    GXA_TRY(attn_fwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, D, S.lse, d.B, d.H, d.Lq, d.Lk, s));
+    GXA_TRY(attn_fwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, D, S.lse, d.B, d.H, d.Lq, d.Lk, s,
+                          make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
     GXA_TRY(gemm_bf16(S.ctx, D, false, W.out, D, false, M, D, D, EPI_GATE_RES, S.x1, D, S.o, D, p.out_proj_b, x, D,
                       p.attn_gate, 0, s));
     x1 = S.x1;
@@ -189,7 +194,7 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   GXA_TRY(gemm_bf16(S.h2, D, false, W.ff0, D, false, M, 4 * D, D, EPI_BIAS_GELU, S.u, 4 * D, S.a, 4 * D, p.ff0_b, nullptr,
                     0, nullptr, 0, s));
   GXA_TRY(gemm_bf16(S.a, 4 * D, false, W.ff2, 4 * D, false, M, D, 4 * D, EPI_GATE_RES, y, D, S.f, D, p.ff2_b, x1, D,
-                    p.ff_gate, 0, s));
+                    p.ff_gate, 0, s, nullptr, make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn)));   // S.f = dropout(f)
   return 0;
 }
 
@@ -230,7 +235,8 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   if (cudaMemsetAsync(Wk.gacc, 0, 64 * sizeof(float), s) != cudaSuccess) return fail(GXA_ERR_CUDA);
   const float* x1 = d.has_xa ? S.x1 : x;
   // ---- FFN branch
-  GXA_TRY(gate_bwd(dy, S.f, 0, p.ff_gate, Wk.gacc + 1, Wk.df, 0, g.ff2_b, M, D, s));
+  GXA_TRY(gate_bwd(dy, S.f, 0, p.ff_gate, Wk.gacc + 1, Wk.df, 0, g.ff2_b, M, D, s,
+                   make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn)));
   GXA_TRY(gemm_bf16(Wk.df, D, false, W.ff2, 4 * D, true, M, 4 * D, D, EPI_GELU_BWD, Wk.du, 4 * D, nullptr, 0, nullptr,
                     S.u, 4 * D, nullptr, 0, s, g.ff0_b));     // d(ff.0.bias) = colsum(du) fused in the epilogue
   GXA_TRY(gemm_bf16(Wk.df, D, true, S.a, 4 * D, true, D, 4 * D, M, EPI_F32, g.ff2_w, 4 * D, nullptr, 0, nullptr, nullptr,
@@ -255,7 +261,8 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
                     nullptr, 1, s));
   // ---- attention core
   GXA_TRY(attn_bwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, Wk.dctx, D, S.lse, Wk.delta, Wk.dq, D,
-                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s, g.in_proj_b));   // + fused d(bq)
+                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s, g.in_proj_b,      // + fused d(bq)
+                        make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
   GXA_TRY(colsum(Wk.dkv, 0, 2 * D, g.in_proj_b + D, Mk, 2 * D, s));
   GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 1, s));
@@ -501,6 +508,14 @@ int gxa_attn_fwd(const void* q, int ldq, const void* k, const void* v, int ldkv,
                         reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
+int gxa_attn_fwd_dropout(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
+                         const int32_t* kv_end, void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk,
+                         float p_drop, uint64_t seed, void* stream) {
+  if (!q || !k || !v || !ctx || !(p_drop >= 0.f && p_drop < 1.f)) return GXA_ERR_ARG;
+  GXA_TRY(attn_fwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, ldc, lse, B, H, Lq, Lk,
+                        reinterpret_cast<cudaStream_t>(stream), make_drop_cfg(p_drop, seed, kDropStreamAttn)));
+  return 0;
+}
 size_t gxa_attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_workspace_bytes(B, H, Lq); }
 
 int gxa_attn_bwd(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
@@ -510,6 +525,18 @@ int gxa_attn_bwd(const void* q, int ldq, const void* k, const void* v, int ldkv,
   if (!q || !k || !v || !ctx || !dctx || !lse || !delta || !dq || !dk || !dv) return GXA_ERR_ARG;
   GXA_TRY(attn_bwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, dctx, ldc, lse, delta, dq, lddq, dk, dv, lddkv, workspace,
                         B, H, Lq, Lk, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+int gxa_attn_bwd_dropout(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask,
+                         const int32_t* kv_end, const void* ctx, const void* dctx, int ldc, const float* lse,
+                         float* delta, void* dq, int lddq, void* dk, void* dv, int lddkv, void* workspace, int B, int H,
+                         int Lq, int Lk, float p_drop, uint64_t seed, void* stream) {
+  if (!q || !k || !v || !ctx || !dctx || !lse || !delta || !dq || !dk || !dv) return GXA_ERR_ARG;
+  if (!(p_drop >= 0.f && p_drop < 1.f)) return GXA_ERR_ARG;
+  GXA_TRY(attn_bwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, dctx, ldc, lse, delta, dq, lddq, dk, dv, lddkv, workspace,
+                        B, H, Lq, Lk, reinterpret_cast<cudaStream_t>(stream), nullptr,
+                        make_drop_cfg(p_drop, seed, kDropStreamAttn)));
   return 0;
 }
 

@@ -413,7 +413,7 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, int ldq, const __nv_bflo
 static inline int chk() { count_launch(); return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA; }
 
 int attn_fwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end, void* ctx,
-                int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s);
+                int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s, DropCfg drop);
 
 // GXA_ATTN=legacy selects the mma.sync kernels (A/B comparison); default is the tcgen05 path
 static bool use_legacy_attn() {
@@ -426,13 +426,14 @@ static bool use_legacy_attn() {
 }
 
 int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
-                  void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s) {
+                  void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s, DropCfg drop) {
   if (B <= 0 || H <= 0 || Lq <= 0 || Lk <= 0) return GXA_ERR_SHAPE;
   if ((ldq % 8) || (ldkv % 8) || (ldc % 8)) return GXA_ERR_ALIGN;
   // tcgen05 path: K|V packed side by side in one [B*Lk, 2D] matrix (the KV projection's natural output)
   if (!use_legacy_attn() && Lk <= 1024 && ldkv == 2 * H * 64 &&
       v == reinterpret_cast<const __nv_bfloat16*>(k) + H * 64 && (reinterpret_cast<uintptr_t>(ctx) & 15) == 0)
-    return attn_fwd_tc(q, ldq, k, ldkv, mask, kv_end, ctx, ldc, lse, B, H, Lq, Lk, s);
+    return attn_fwd_tc(q, ldq, k, ldkv, mask, kv_end, ctx, ldc, lse, B, H, Lq, Lk, s, drop);
+  if (drop.thresh != 0) return GXA_ERR_UNSUPPORTED;     // dropout exists on the tcgen05 path only
   dim3 grid((Lq + AT - 1) / AT, H, B);
   attn_fwd_kernel<<<grid, ATT_THREADS, 0, s>>>(
       reinterpret_cast<const __nv_bfloat16*>(q), ldq, reinterpret_cast<const __nv_bfloat16*>(k),
@@ -446,7 +447,7 @@ int attn_bwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t*
                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, cudaStream_t s);
 int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
                  const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
-                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s);
+                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s, DropCfg drop);
 size_t attn_bwd_tc_workspace(int B, int H, int Lq);
 
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_tc_workspace(B, H, Lq); }
@@ -454,7 +455,7 @@ size_t attn_bwd_workspace_bytes(int B, int H, int Lq) { return attn_bwd_tc_works
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
                   void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s,
-                  float* dq_colsum) {
+                  float* dq_colsum, DropCfg drop) {
   if (B <= 0 || H <= 0 || Lq <= 0 || Lk <= 0) return GXA_ERR_SHAPE;
   if ((ldq % 8) || (ldkv % 8) || (ldc % 8) || (lddq % 8) || (lddkv % 8)) return GXA_ERR_ALIGN;
   auto Q = reinterpret_cast<const __nv_bfloat16*>(q);
@@ -470,10 +471,11 @@ int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
   static const bool bwd_v1 = getenv("GXA_ATTN_BWD") && getenv("GXA_ATTN_BWD")[0] == '1';   // A/B: per-item CTAs
   if (!use_legacy_attn() && packed && !bwd_v1)       // persistent tcgen05 kernel (any Lq, Lk)
     return attn_bwd_tc2(q, ldq, k, ldkv, mask, kv_end, dctx, ldc, lse, delta, reinterpret_cast<float*>(workspace), dq,
-                        lddq, dk, dv, lddkv, B, H, Lq, Lk, dq_colsum, s);
+                        lddq, dk, dv, lddkv, B, H, Lq, Lk, dq_colsum, s, drop);
+  if (drop.thresh != 0) return GXA_ERR_UNSUPPORTED;     // dropout exists on the persistent tcgen05 path only
   if (dq_colsum != nullptr) {     // the other paths have no fused d(bq): one pass over dq afterwards
     const int e = attn_bwd_bf16(q, ldq, k, v, ldkv, mask, kv_end, ctx, dctx, ldc, lse, delta, dq, lddq, dk, dv, lddkv,
-                                workspace, B, H, Lq, Lk, s, nullptr);
+                                workspace, B, H, Lq, Lk, s, nullptr, drop);
     return e ? e : colsum(dq, 0, lddq, dq_colsum, B * Lq, H * 64, s);
   }
   if (!use_legacy_attn() && packed && Lk <= 1024 && Lq <= 1024)

@@ -73,7 +73,7 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                     const __grid_constant__ CUtensorMap tmDO, const uint8_t* __restrict__ mask,
                     const int* __restrict__ kv_end, const float* __restrict__ lse, const float* __restrict__ delta,
                     float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dk, __nv_bfloat16* __restrict__ dv, int lddkv,
-                    int B, int H, int Lq, int Lk, int D, int LqPad, long long* dbg) {
+                    int B, int H, int Lq, int Lk, int D, int LqPad, const DropCfg drop, long long* dbg) {
 #define STAMP(role, k) do { if (dbg && blockIdx.x == 0 && g < 16 && lane == 0) dbg[(role) * 128 + g * 8 + (k)] = clock64(); } while (0)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
@@ -297,8 +297,25 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
           for (int c = 0; c < 32; ++c) pv[c] = ex2a(fmaf(__uint_as_float(sr[c]) + kbias[c], kScaleLog2, nls));
         }
+        if (drop.thresh == 0) {
 #pragma unroll
-        for (int c = 0; c < 32; ++c) dsv[c] = pv[c] * (__uint_as_float(dr[c]) - de);
+          for (int c = 0; c < 32; ++c) dsv[c] = pv[c] * (__uint_as_float(dr[c]) - de);
+        } else {
+          // dropout on the probabilities (forward: ctx = (m*P) V): dV sees m*P, dP = m * (dO V^T); same mask as forward
+          const uint32_t ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) *
+                                   static_cast<uint32_t>((Lk + 1) >> 1) + ((cur.k0 + cq * 32) >> 1);
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            bool k0, k1;
+            drop_keep(drop, ctr + c, k0, k1);
+            // dS = P*(m*dP - delta) = (m*P)*dP - P*delta ;  the P tile for dV holds m*P
+            const float t0 = pv[2 * c] * de, t1 = pv[2 * c + 1] * de;
+            pv[2 * c] = k0 ? pv[2 * c] * drop.scale : 0.f;
+            pv[2 * c + 1] = k1 ? pv[2 * c + 1] * drop.scale : 0.f;
+            dsv[2 * c] = fmaf(pv[2 * c], __uint_as_float(dr[2 * c]), -t0);
+            dsv[2 * c + 1] = fmaf(pv[2 * c + 1], __uint_as_float(dr[2 * c + 1]), -t1);
+          }
+        }
         if (warp == 0) STAMP(1, 2);
         if (g > 0) mbar_wait(&sm.pds_free, (g - 1) & 1);     // previous dV/dK/dQ MMAs no longer read P / dS
 #pragma unroll
@@ -501,7 +518,7 @@ size_t attn_bwd_tc_workspace(int B, int H, int Lq);
 // Persistent backward (see the header of this file).  Same contract as attn_bwd_tc.
 int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
                  const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
-                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s) {
+                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s, DropCfg drop) {
   const int D = H * HD;
   const int LqPad = (Lq + BQ - 1) / BQ * BQ;
   CUtensorMap tmQ, tmKV, tmDO;
@@ -520,7 +537,7 @@ int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t
   if ((total + grid - 1) / grid > MAX_ITEMS) grid = (total + MAX_ITEMS - 1) / MAX_ITEMS;
   attn_bwd_tc2_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(tmQ, tmKV, tmDO, mask, kv_end, lse, delta, dq_acc,
                                                         reinterpret_cast<__nv_bfloat16*>(dk),
-                                                        reinterpret_cast<__nv_bfloat16*>(dv), lddkv, B, H, Lq, Lk, D, LqPad,
+                                                        reinterpret_cast<__nv_bfloat16*>(dv), lddkv, B, H, Lq, Lk, D, LqPad, drop,
                                                         getenv("GXA_DBG_PTR") ? reinterpret_cast<long long*>(strtoull(getenv("GXA_DBG_PTR"), nullptr, 0)) : nullptr);
   count_launch();
   if (cudaGetLastError() != cudaSuccess) return GXA_ERR_CUDA;

@@ -53,7 +53,7 @@ __device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 2
 __global__ void __launch_bounds__(TC_FWD_THREADS, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                    const uint8_t* __restrict__ mask, const int* __restrict__ kv_end, __nv_bfloat16* __restrict__ ctx,
-                   int ldc, float* __restrict__ lse, int H, int Lq, int Lk, int D) {
+                   int ldc, float* __restrict__ lse, int H, int Lq, int Lk, int D, const DropCfg drop) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];   // direct use keeps the shared state space (LDS/STS, not generic)
   FwdTcSmem& sm = *reinterpret_cast<FwdTcSmem*>(smem_raw);
   if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
@@ -152,10 +152,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int r = quarter * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
     float m = -INFINITY, l = 0.f;
+    const float drop_log2 = drop.thresh != 0 ? log2f(drop.scale) : 0.f;
     float o[32];
 #pragma unroll
     for (int i = 0; i < 32; ++i) o[i] = 0.f;
     const uint32_t p_row = smem_u32(sm.p) + half * TC_TILE + r * 128;     // this thread's 64 keys = swizzle atom `half`
+    // dropout counter of this query row: (b, h, q) * ceil(Lk / 2) + key / 2   (gxa_rng.cuh)
+    const uint32_t drop_row = (static_cast<uint32_t>(b * H + h) * Lq + (q0 + r)) * static_cast<uint32_t>((Lk + 1) >> 1);
 
     for (int j = 0; j < nblk; ++j) {
       const float* kb = sm.kbias + j * TC_BK + half * 64;
@@ -196,7 +199,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       l *= alpha;
       m = m_new;
       // ---- pass 2: p = exp2((s - m) * scale*log2e), partial row sum, bf16 P tile
-      const float mneg = -m_use * kScaleLog2_tc;
+      const float mneg = -m_use * kScaleLog2_tc + drop_log2;    // dropout: p carries the 1/(1-p) factor
 #pragma unroll
       for (int c = 0; c < 64; c += 32) {
         uint32_t sr[32];
@@ -213,6 +216,17 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) l += pv[i];
+        if (drop.thresh != 0) {      // dropout on the probabilities: the row sum above stays undropped (softmax first);
+          // the 1/(1-p) factor is already in pv (folded into the exponent), so dropping is one select per element
+          const uint32_t ctr = drop_row + ((j * TC_BK + half * 64 + c) >> 1);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            bool k0, k1;
+            drop_keep(drop, ctr + i, k0, k1);
+            pv[2 * i] = k0 ? pv[2 * i] : 0.f;
+            pv[2 * i + 1] = k1 ? pv[2 * i + 1] : 0.f;
+          }
+        }
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const int chunk = (c >> 3) + g;
@@ -235,6 +249,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     sm.psum[half][r] = l;
     softmax_bar_sync();
     l += sm.psum[half ^ 1][r];
+    if (drop.thresh != 0) l *= 1.0f / drop.scale;      // back to the plain softmax denominator; O keeps the factor
     const float inv = l > 0.f ? 1.0f / l : 0.f;
     if (nblk > 0) {
       mbar_wait(&sm.pv_done, (nblk - 1) & 1);
@@ -264,7 +279,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 }
 
 int attn_fwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end, void* ctx,
-                int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s) {
+                int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s, DropCfg drop) {
   const int D = H * TC_HD;
   if (Lk > TC_MAXK) return GXA_ERR_UNSUPPORTED;
   CUtensorMap tmQ, tmKV;
@@ -278,7 +293,7 @@ int attn_fwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t*
   }
   dim3 grid((Lq + TC_BQ - 1) / TC_BQ, H, B);
   attn_fwd_tc_kernel<<<grid, TC_FWD_THREADS, FWD_TC_SMEM, s>>>(tmQ, tmKV, mask, kv_end, reinterpret_cast<__nv_bfloat16*>(ctx), ldc,
-                                                    lse, H, Lq, Lk, D);
+                                                    lse, H, Lq, Lk, D, drop);
   count_launch();
   return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }

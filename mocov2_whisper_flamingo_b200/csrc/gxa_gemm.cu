@@ -274,7 +274,7 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
   GemmParams p;
   p.M = op.M; p.N = op.N; p.K = op.K;
   p.C = op.C; p.ldc = op.ldc; p.C2 = op.C2; p.ldc2 = op.ldc2;
-  p.bias = op.bias; p.aux = op.aux; p.ld_aux = op.ld_aux; p.gate = op.gate; p.accumulate = op.accumulate; p.colsum = op.colsum;
+  p.bias = op.bias; p.aux = op.aux; p.ld_aux = op.ld_aux; p.gate = op.gate; p.accumulate = op.accumulate; p.colsum = op.colsum; p.drop = op.drop;
   const int kb_total = (op.K + GEMM_BK - 1) / GEMM_BK;
   int bn = op.bn;
   if (bn == 0) {
@@ -308,6 +308,7 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
     }
   }
   if (op.colsum != nullptr && op.epi != EPI_GELU_BWD) return GXA_ERR_UNSUPPORTED;
+  if (op.drop.thresh != 0 && op.epi != EPI_GATE_RES) return GXA_ERR_UNSUPPORTED;
   if (pair) return gemm2_launch(op, p, stream);
   int e = GXA_ERR_UNSUPPORTED;
   if (bn == 256) e = launch_epi<256>(op, p, stream);

@@ -14,6 +14,7 @@
 // epilogue of tile i overlaps the main loop of tile i+1.  Grid = min(#work, #SMs).
 #pragma once
 #include "gxa_ptx.cuh"
+#include "gxa_rng.cuh"
 
 namespace gxa {
 
@@ -37,6 +38,7 @@ struct GemmParams {
   int ld_aux;
   const float* gate;   // device scalar, tanh applied in-kernel
   int accumulate;
+  DropCfg drop;        // EPI_GATE_RES: dropout on t before it is stored / gated (nn.Dropout after ff.2); thresh 0 = off
   float* colsum;       // EPI_GELU_BWD: colsum[n] += sum over rows of the (bf16-rounded) output, i.e. the bias gradient
 };
 
@@ -112,6 +114,16 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
   } else if constexpr (EPI == EPI_GATE_RES) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = bf16r(v[i]);
+    if (p.drop.thresh != 0) {
+      const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N >> 1) + (col >> 1);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        float m0, m1;
+        drop_pair(p.drop, ctr + i, m0, m1);
+        v[2 * i] = bf16r(v[2 * i] * m0);
+        v[2 * i + 1] = bf16r(v[2 * i + 1] * m1);
+      }
+    }
     store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + col, v);
     const float4* x4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) +
                                                        static_cast<size_t>(row) * p.ld_aux + col);
@@ -275,8 +287,16 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
       if (p.accumulate || p.k_splits > 1) atomicAdd(dst, a);
       else *dst = a;
     } else if constexpr (EPI == EPI_GATE_RES) {
-      const uint2 pk = pack_bf16x4(a);
+      uint2 pk = pack_bf16x4(a);
       a = unpack_bf16x4(pk);
+      if (p.drop.thresh != 0) {      // bf16(linear) -> dropout -> bf16, as autocast does
+        const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N >> 1) + (c >> 1);
+        float m0, m1, m2, m3;
+        drop_pair(p.drop, ctr, m0, m1);
+        drop_pair(p.drop, ctr + 1, m2, m3);
+        pk = pack_bf16x4(make_float4(a.x * m0, a.y * m1, a.z * m2, a.w * m3));
+        a = unpack_bf16x4(pk);
+      }
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) = pk;
       const float4 x = ax.v[it];
       *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + off) =

@@ -6,6 +6,7 @@
 #include <stdint.h>
 
 #include "../../include/gxa.h"
+#include "gxa_rng.cuh"
 
 namespace gxa {
 
@@ -29,6 +30,7 @@ struct GemmOp {
   const void* aux = nullptr; int ld_aux = 0;
   const float* gate = nullptr;
   int accumulate = 0;
+  DropCfg drop = DropCfg{0, 1.f, 0, 0};   // EPI_GATE_RES only: dropout on the linear output
   float* colsum = nullptr;   // EPI_GELU_BWD only: += column sums of the output (fused bias gradient)
   int bn = 0;        // 0 = choose
   int k_splits = 0;  // 0 = choose
@@ -49,7 +51,7 @@ int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const fl
            float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s);
 // dout = tanh(gate) * dy ; dgate_accum += sum(dy * f) ; dbias += colsum(dout)
 int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, float* dgate_accum, void* dout,
-             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s);
+             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s, DropCfg drop = DropCfg{0, 1.f, 0, 0});
 int gate_finish(const float* gate, const float* accum, float* dgate, cudaStream_t s);   // dgate = (1-tanh^2) * accum
 int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, cudaStream_t s);   // dst += colsum
 int cast_f32_bf16(const float* src, void* dst, size_t n, cudaStream_t s);
@@ -65,11 +67,13 @@ int add_inplace_f32(float* dst, const float* src, size_t n, cudaStream_t s);
 
 // ---- attention (gxa_attn.cu: bf16 tensor-core path; gxa_attn_f32.cu: fp32 accuracy path)
 int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
-                  void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s);
+                  void* ctx, int ldc, float* lse, int B, int H, int Lq, int Lk, cudaStream_t s,
+                  DropCfg drop = DropCfg{0, 1.f, 0, 0});
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
                   void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s,
-                  float* dq_colsum = nullptr);   // optional: += column sums of dq (fused bias gradient)
+                  float* dq_colsum = nullptr,    // optional: += column sums of dq (fused bias gradient)
+                  DropCfg drop = DropCfg{0, 1.f, 0, 0});
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq);
 int attn_fwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const uint8_t* mask, float* ctx,
                  int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s);

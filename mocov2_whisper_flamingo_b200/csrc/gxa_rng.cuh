@@ -19,20 +19,26 @@ struct DropCfg {
   uint32_t seed_lo, seed_hi;
 };
 
+// two multiply-fold rounds (64-bit product, high ^ low): 2 IMAD.WIDE + 2 LOP3 per 32 random bits
 __host__ __device__ __forceinline__ uint32_t drop_mix(uint32_t ctr, uint32_t seed_lo, uint32_t seed_hi) {
-  uint32_t x = ctr ^ seed_lo;
-  x ^= x >> 16; x *= 0x7feb352dU;
-  x ^= x >> 15; x *= 0x846ca68bU;
-  x ^= x >> 16;
-  x = (x ^ seed_hi) * 0x9E3779B1U;
-  x ^= x >> 15;
-  return x;
+  uint64_t t = static_cast<uint64_t>(ctr ^ seed_lo) * 0x9E3779B1ULL;
+  const uint32_t y = static_cast<uint32_t>(t >> 32) ^ static_cast<uint32_t>(t) ^ seed_hi;
+  t = static_cast<uint64_t>(y) * 0x85EBCA77ULL;
+  return static_cast<uint32_t>(t >> 32) ^ static_cast<uint32_t>(t);
 }
-// scale factors (0 or cfg.scale) for the column pair (2*pair, 2*pair + 1) of a row whose pair counter starts at row_ctr
-__device__ __forceinline__ void drop_pair(const DropCfg& c, uint32_t ctr, float& m0, float& m1) {
+// keep decisions for the column pair (2*pair, 2*pair + 1):  u16 >= thresh, evaluated on the full word
+__device__ __forceinline__ void drop_keep(const DropCfg& c, uint32_t ctr, bool& k0, bool& k1) {
   const uint32_t x = drop_mix(ctr, c.seed_lo, c.seed_hi);
-  m0 = (x & 0xffffu) >= c.thresh ? c.scale : 0.f;
-  m1 = (x >> 16) >= c.thresh ? c.scale : 0.f;
+  const uint32_t t = c.thresh << 16;
+  k0 = (x << 16) >= t;
+  k1 = x >= t;
+}
+// multipliers (0 or cfg.scale) for the same pair
+__device__ __forceinline__ void drop_pair(const DropCfg& c, uint32_t ctr, float& m0, float& m1) {
+  bool k0, k1;
+  drop_keep(c, ctr, k0, k1);
+  m0 = k0 ? c.scale : 0.f;
+  m1 = k1 ? c.scale : 0.f;
 }
 inline DropCfg make_drop_cfg(float p, uint64_t seed, uint32_t stream) {
   DropCfg c;

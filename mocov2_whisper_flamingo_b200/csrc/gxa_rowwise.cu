@@ -371,7 +371,7 @@ template <int NV>
 __global__ void __launch_bounds__(RW_WARPS * 32)
 gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_is_f32, const float* __restrict__ gate,
                 float* __restrict__ dgate_accum, void* __restrict__ dout, int out_is_f32, float* __restrict__ dbias,
-                int rows) {
+                int rows, const DropCfg drop) {
   constexpr int D = 128 * NV;
   extern __shared__ float sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -389,6 +389,13 @@ gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_
       float4 fv = ld4_any(f, base + c, f_is_f32);
       gacc += d.x * fv.x + d.y * fv.y + d.z * fv.z + d.w * fv.w;
       float4 t = make_float4(gate_t * d.x, gate_t * d.y, gate_t * d.z, gate_t * d.w);
+      if (drop.thresh != 0) {     // backward of nn.Dropout after ff.2: the forward mask, re-created from (seed, element)
+        const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(D >> 1) + (c >> 1);
+        float m0, m1, m2, m3;
+        drop_pair(drop, ctr, m0, m1);
+        drop_pair(drop, ctr + 1, m2, m3);
+        t.x *= m0; t.y *= m1; t.z *= m2; t.w *= m3;
+      }
       if (!out_is_f32) {
         t.x = __bfloat162float(__float2bfloat16_rn(t.x)); t.y = __bfloat162float(__float2bfloat16_rn(t.y));
         t.z = __bfloat162float(__float2bfloat16_rn(t.z)); t.w = __bfloat162float(__float2bfloat16_rn(t.w));
@@ -403,14 +410,14 @@ gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_
 }
 
 int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, float* dgate_accum, void* dout,
-             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s) {
+             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s, DropCfg drop) {
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
   const size_t smem = sizeof(float) * RW_WARPS * D;
   int grid = 1;
   GXA_NV_DISPATCH(D, (grid = resident_grid(gate_bwd_kernel<NV>, smem, rows, RW_WARPS)));
   GXA_NV_DISPATCH(D, (gate_bwd_kernel<NV><<<grid, RW_WARPS * 32, smem, s>>>(dy, f, f_is_f32, gate, dgate_accum, dout,
-                                                                            out_is_f32, dbias, rows)));
+                                                                            out_is_f32, dbias, rows, drop)));
   return check_launch();
 }
 

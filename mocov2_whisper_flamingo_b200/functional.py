@@ -126,22 +126,34 @@ class StackShared:
                       "gxa_mask_prepare")
 
 
-def _dims(B, Lq, Lk, D, H, precision, has_xa) -> Dims:
-    return Dims(B=B, Lq=Lq, Lk=max(Lk, 0), D=D, H=H, precision=precision, has_xa=int(has_xa), reserved=0)
+def _dims(B, Lq, Lk, D, H, precision, has_xa, p_drop=0.0, seed=0) -> Dims:
+    return Dims(B=B, Lq=Lq, Lk=max(Lk, 0), D=D, H=H, precision=precision, has_xa=int(has_xa), reserved=0,
+                p_drop=float(p_drop), reserved2=0, seed=int(seed) & 0xFFFFFFFFFFFFFFFF)
+
+
+# Dropout seeds: the masks are a pure function of (seed, element) (csrc/gxa_rng.cuh), so all the host has to supply is
+# one fresh 64-bit seed per (forward call, layer).  It is drawn from torch's default CPU generator: reproducible under
+# torch.manual_seed(), advances with every call, and costs no kernel launch or device sync.
+def next_dropout_seed() -> int:
+    hi, lo = torch.randint(0, 1 << 31, (2,), dtype=torch.int64).tolist()
+    return ((hi << 33) ^ (lo << 2) ^ 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
 
 
 class BlockFn(torch.autograd.Function):
     """GatedCrossAttentionBlock.forward / backward (reference: models/gate_cross_attention.py:28-50)."""
 
     @staticmethod
-    def forward(ctx, x, xa, shared: StackShared, state: BlockState, n_heads: int, token, *params):
+    def forward(ctx, x, xa, shared: StackShared, state: BlockState, n_heads: int, token, p_drop: float, *params):
         L = _lib.lib()
         _require_cuda(x, "x")
         B, Lq, D = x.shape
         xf = _f32c(x)
         has_xa = xa is not None
         Lk = xa.shape[1] if has_xa else 0
-        dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa)
+        if p_drop > 0.0 and shared.precision != GXA_PREC_BF16:
+            raise NotImplementedError("gxa_b200: training-mode dropout is implemented for the bf16 (autocast) precision "
+                                      "only; use torch.autocast / set_default_precision('bf16'), dropout=0.0 or .eval()")
+        dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa, p_drop, next_dropout_seed() if p_drop > 0.0 else 0)
         pd = [p.detach() for p in params]
         for p in pd:
             if p.dtype != torch.float32 or not p.is_contiguous():
@@ -207,7 +219,7 @@ class BlockFn(torch.autograd.Function):
         if not dims.has_xa:           # attention parameters did not take part (reference: grad None)
             for i in (0, 2, 3, 4, 5, 6, 7):
                 grads[i] = None
-        return (dx.to(ctx.x_dtype) if ctx.x_dtype != torch.float32 else dx, dxa, None, None, None, None, *grads)
+        return (dx.to(ctx.x_dtype) if ctx.x_dtype != torch.float32 else dx, dxa, None, None, None, None, None, *grads)
 
 
 class LayerNormFn(torch.autograd.Function):

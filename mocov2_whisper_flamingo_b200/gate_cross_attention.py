@@ -74,13 +74,12 @@ class GatedCrossAttentionBlock(nn.Module):
             xa = xa.squeeze(1)
         if mask is not None and mask.dim() == 3 and mask.size(1) == 1:
             mask = mask.squeeze(1)
-        if self.training and self.dropout > 0.0:
-            raise NotImplementedError("gxa_b200: dropout > 0 in training mode is not implemented yet "
-                                      "(construct with dropout=0.0 or call .eval())")
+        # dropout (reference :16 attention probabilities, :26 after ff.2) is active in training mode only
+        p_drop = float(self.dropout) if self.training else 0.0
         shared = _shared
         if shared is None:
             shared = StackShared(xa, mask if xa is not None else None, resolve_precision(self.precision))
-        y = BlockFn.apply(x, xa, shared, self._state, self.n_heads, self, *self._params())
+        y = BlockFn.apply(x, xa, shared, self._state, self.n_heads, self, p_drop, *self._params())
         if self.enable_logging:
             logger.info(f"GatedCrossAttentionBlock output shape: {y.shape}")
         return y

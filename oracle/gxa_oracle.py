@@ -157,8 +157,11 @@ def _merge_heads(t):
     return t.transpose(0, 2, 1, 3).reshape(B, L, H * hd)
 
 
-def block_forward(p, x, xa, mask, n_heads):
-    """One GatedCrossAttentionBlock forward, dropout = 0 (gate_cross_attention.py:28-50).
+def block_forward(p, x, xa, mask, n_heads, drop=None):
+    """One GatedCrossAttentionBlock forward (gate_cross_attention.py:28-50).
+
+    drop: None (eval / dropout = 0) or (attn_m [B,H,Lq,Lk], ffn_m [B,Lq,D]): the training-mode dropout multipliers
+    (0 or 1/(1-p)) applied to the attention probabilities inside SDPA (:16) and to the ff.2 output (:26).
 
     p: dict of the 14 block tensors.  mask: bool [B,Lk], True = key ignored, or None.
     xa None => FFN only (:39).  Returns (y, cache)."""
@@ -189,20 +192,25 @@ def block_forward(p, x, xa, mask, n_heads):
         den = e.sum(-1, keepdims=True)
         # fully masked row: torch 2.11 SDPA yields a zero context
         Pm = np.where(den > 0, e / np.where(den > 0, den, 1.0), 0.0)
-        ctx = _merge_heads(np.einsum("bhqk,bhkd->bhqd", Pm, vh))
+        attn_m = None if drop is None else _f64(drop[0])
+        Pd = Pm if attn_m is None else Pm * attn_m
+        ctx = _merge_heads(np.einsum("bhqk,bhkd->bhqd", Pd, vh))
         o = ctx @ P["attn.out_proj.weight"].T + P["attn.out_proj.bias"]
         ga = math.tanh(float(P["attn_gate"][0]))
         x1 = x + ga * o
-        c.update(xa=xa, mask=mask, h=h, qh=qh, kh=kh, vh=vh, P=Pm, ctx=ctx, o=o, ga=ga)
+        c.update(xa=xa, mask=mask, h=h, qh=qh, kh=kh, vh=vh, P=Pm, Pd=Pd, attn_m=attn_m, ctx=ctx, o=o, ga=ga)
     else:
         x1 = x
     h2, c["ln2"] = ln_fwd(x1, P["ff_ln.weight"], P["ff_ln.bias"])
     u = h2 @ P["ff.0.weight"].T + P["ff.0.bias"]
     a = gelu_fwd(u)
     f = a @ P["ff.2.weight"].T + P["ff.2.bias"]
+    ffn_m = None if drop is None else _f64(drop[1])
+    if ffn_m is not None:
+        f = f * ffn_m
     gf = math.tanh(float(P["ff_gate"][0]))
     y = x1 + gf * f
-    c.update(x1=x1, h2=h2, u=u, a=a, f=f, gf=gf, has_attn=xa is not None)
+    c.update(x1=x1, h2=h2, u=u, a=a, f=f, gf=gf, ffn_m=ffn_m, has_attn=xa is not None)
     return y, c
 
 
@@ -217,6 +225,8 @@ def block_backward(p, c, dy):
     gf = c["gf"]
     g["ff_gate"] = np.array([(1 - gf * gf) * (dy * c["f"]).sum()])
     df = gf * dy
+    if c.get("ffn_m") is not None:
+        df = df * c["ffn_m"]
     g["ff.2.weight"] = flat(df).T @ flat(c["a"])
     g["ff.2.bias"] = flat(df).sum(0)
     da = df @ P["ff.2.weight"]
@@ -239,8 +249,10 @@ def block_backward(p, c, dy):
     dctx = _split_heads(do @ P["attn.out_proj.weight"], H)
     Pm, qh, kh, vh = c["P"], c["qh"], c["kh"], c["vh"]
     scale = 1.0 / math.sqrt(D // H)
-    dv = np.einsum("bhqk,bhqd->bhkd", Pm, dctx)
+    dv = np.einsum("bhqk,bhqd->bhkd", c.get("Pd", Pm), dctx)
     dP = np.einsum("bhqd,bhkd->bhqk", dctx, vh)
+    if c.get("attn_m") is not None:
+        dP = dP * c["attn_m"]
     delta = (dP * Pm).sum(-1, keepdims=True)
     dS = Pm * (dP - delta)
     dq = _merge_heads(np.einsum("bhqk,bhkd->bhqd", dS, kh)) * scale

@@ -123,3 +123,55 @@ def test_state_dict_layout_matches_reference_order():
     assert list(blk.state_dict().keys()) == list(O.BLOCK_KEYS)
     fus = G.GatedCrossModalFusion(128, 2, 3, dropout=0.0)
     assert list(fus.state_dict().keys()) == list(O.fusion_param_shapes(128, 3).keys())
+
+
+# ---------------------------------------------------------------------------------------------- dropout (training mode)
+def test_block_dropout_training_matches_oracle_with_same_masks(monkeypatch):
+    """Training-mode dropout (reference: nn.MultiheadAttention(dropout=p) and nn.Dropout(p) after ff.2).  torch's own
+    RNG stream cannot be reproduced (nor does the reference reproduce across devices), so parity is checked against the
+    float64 oracle fed with the masks the kernels derive from the seed (tests/dropout_ref.py)."""
+    import dropout_ref as DR
+    from mocov2_whisper_flamingo_b200 import functional as F
+    B, Lq, Lk, D, H, p_drop, seed = 2, 96, 81, 256, 4, 0.1, 0xC0FFEE1234567
+    monkeypatch.setattr(F, "next_dropout_seed", lambda: seed)
+    p = O.make_params(O.block_param_shapes(D), 11)
+    x, xa, mask, dy = O.make_inputs(B, Lq, Lk, D, 11, lengths=[81, 40])
+    drop = (DR.attn_multipliers(B, H, Lq, Lk, p_drop, seed), DR.ffn_multipliers(B, Lq, D, p_drop, seed))
+    yo, c = O.block_forward(p, x, xa, mask, H, drop=drop)
+    go, dxo, dxao = O.block_backward(p, c, dy)
+    mod = G.GatedCrossAttentionBlock(D, H, dropout=p_drop)
+    mod.load_state_dict({k: torch.from_numpy(v) for k, v in p.items()}, strict=True)
+    mod.cuda().train()
+    y, dx, dxa, grads = run(mod, "block", x, xa, mask, dy, "bf16")
+    y0, _ = O.block_forward(p, x, xa, mask, H)
+    assert rel_err(torch.from_numpy(yo), torch.from_numpy(y0)) > 5e-2            # the masks matter at this tolerance
+    assert rel_err(y.cpu(), torch.from_numpy(yo)) < 2e-2
+    assert rel_err(dx.cpu(), torch.from_numpy(dxo)) < 3e-2
+    assert rel_err(dxa.cpu(), torch.from_numpy(dxao)) < 3e-2
+    assert np.all(dxa.cpu().numpy()[mask] == 0)
+    for k, v in go.items():
+        compare_grad(k, grads[k], v, 3e-2)
+    # eval mode: dropout is off and the result equals the dropout = 0 module bit for bit
+    mod.eval()
+    ye, *_ = run(mod, "block", x, xa, mask, dy, "bf16")
+    ref0 = build("block", D, H, 1, p)
+    y00, *_ = run(ref0, "block", x, xa, mask, dy, "bf16")
+    assert torch.equal(ye, y00)
+
+
+def test_block_dropout_fresh_mask_per_call_and_fp32_unsupported():
+    B, Lq, Lk, D, H = 2, 64, 64, 128, 2
+    p = O.make_params(O.block_param_shapes(D), 3)
+    x, xa, mask, dy = O.make_inputs(B, Lq, Lk, D, 3)
+    mod = G.GatedCrossAttentionBlock(D, H, dropout=0.1)
+    mod.load_state_dict({k: torch.from_numpy(v) for k, v in p.items()}, strict=True)
+    mod.cuda().train()
+    torch.manual_seed(99)
+    y1, *_ = run(mod, "block", x, xa, mask, dy, "bf16")
+    y2, *_ = run(mod, "block", x, xa, mask, dy, "bf16")
+    torch.manual_seed(99)
+    y3, *_ = run(mod, "block", x, xa, mask, dy, "bf16")
+    assert not torch.equal(y1, y2)          # every call draws a new mask ...
+    assert torch.equal(y1, y3)              # ... and torch.manual_seed() makes the sequence reproducible
+    with pytest.raises(NotImplementedError):
+        run(mod, "block", x, xa, mask, dy, "fp32")
