@@ -90,7 +90,7 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads, sample_B=2, sample_layers=2, reps=3):
+def cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads, sample_B=2, sample_layers=2, reps=3, dropout=0.1):
     """The reference's CPU path (oracle/torch_port.py: same ATen CPU kernels as the reference module) on a bounded
     sample: `sample_layers` layers of the stack at batch `sample_B`, fwd+bwd, extrapolated linearly to `layers`."""
     from oracle import gxa_oracle as O
@@ -103,7 +103,7 @@ def cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads, sample_B=2, sample_laye
     times = []
     for i in range(reps + 1):
         t0 = time.perf_counter()
-        y = TP.fusion_forward(p, xt, xat, mt, H, sample_layers)
+        y = TP.fusion_forward(p, xt, xat, mt, H, sample_layers, dropout, True)
         y.backward(dyt)
         times.append(time.perf_counter() - t0)
     t = statistics.median(times[1:])
@@ -129,7 +129,7 @@ def run_reference(args, D, H, layers, GB, Lq, Lk):
     mt, dyt = torch.from_numpy(mask), torch.from_numpy(dy)
 
     def step():
-        TP.fusion_forward(p, xt, xat, mt, H, sample_layers).backward(dyt)
+        TP.fusion_forward(p, xt, xat, mt, H, sample_layers, args.dropout, True).backward(dyt)
 
     for _ in range(args.warmup):
         step()
@@ -147,7 +147,7 @@ def run_reference(args, D, H, layers, GB, Lq, Lk):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "d_model": D, "heads": H, "layers": layers, "global_batch": GB,
-                   "Lq": Lq, "Lk": Lk},
+                   "Lq": Lq, "Lk": Lk, "dropout": args.dropout, "mode": "train"},
         "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -184,7 +184,10 @@ def time_dominant_kernel(M, D, pk):
     return {"bound": "tensor", "kernel": "gemm_tc_kernel<BN=256, EPI_BIAS_GELU> (FFN1 + bias + erf-GELU, M=%d N=%d K=%d)" % (M, N, K),
             "achieved": tf, "peak": pk["burst"], "unit": "TFLOP/s", "frac": tf / pk["burst"],
             "peak_source": pk["source"] + " bf16_tflops (burst: kernel timed alone)", "ms_per_launch": ms,
-            "traffic": None}
+            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this shape, one ncu --set full capture
+            # (profiles/r01_c_ncu_gemm_pair.txt: 67.7 MB read + 417.6 MB written); other shapes were not captured
+            "traffic": 485.3e6 if (M, N, K) == (28672, 4096, 1024) else None,
+            "algorithmic_bytes": 2.0 * (M * K + N * K + 2 * M * N)}
 
 
 def run_product(args, D, H, layers, GB, Lq, Lk):
@@ -202,7 +205,7 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
     b0, b1 = shard_batch(GB, rank, world)
     B = b1 - b0
     torch.manual_seed(1234)
-    model = G.GatedCrossModalFusion(D, H, layers, dropout=0.0)
+    model = G.GatedCrossModalFusion(D, H, layers, dropout=args.dropout)   # reference default: config.py:21 fusion_dropout 0.1
     with torch.no_grad():                      # non-trivial biases / LN affine, nonzero gates
         for n, p in model.named_parameters():
             if n.endswith("attn_gate"):
@@ -287,7 +290,7 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
             "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": args.workload, "d_model": D, "heads": H, "layers": layers, "global_batch": GB,
-                       "per_gpu_batch": B, "Lq": Lq, "Lk": Lk, "parallelism": f"dp{world}", "dropout": 0.0,
+                       "per_gpu_batch": B, "Lq": Lq, "Lk": Lk, "parallelism": f"dp{world}", "dropout": args.dropout, "mode": "train",
                        "step": "fwd + bwd (dgrad+wgrad) + weight bf16 re-cast" + (" + per-layer NCCL grad all-reduce" if world > 1 else ""),
                        "l2": "per-step working set (>30 GB of activations) far exceeds the 126 MB L2; no flush needed"},
             "clocks": clocks, "gpu_launches": launches,
@@ -305,7 +308,7 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            v, t, sample = cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads)
+            v, t, sample = cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads, dropout=args.dropout)
             out["cpu_baseline"] = {"value": v, "unit": "tokens/s", "cores": threads, "kind": "port", "sample": sample,
                                    "seconds_per_sample": t}
         print(json.dumps(out))
@@ -321,6 +324,7 @@ def main():
     ap.add_argument("--impl", default="gxa", choices=["gxa", "reference"])
     ap.add_argument("--workload", default="whisper-medium-c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dropout", type=float, default=0.1, help="training-mode dropout of the stack (reference config.py: 0.1)")
     args = ap.parse_args()
     D, H, layers, GB, Lq, Lk = WORKLOADS[args.workload]
     if args.impl == "reference":

@@ -71,7 +71,7 @@ def test_error_conventions():
         blk(torch.randn(1, 4, 128), torch.randn(1, 4, 128))
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         G.LayerNorm(128)(torch.randn(2, 128))
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError, match="no CPU fallback"):       # training-mode dropout is on the CUDA path too
         G.GatedCrossAttentionBlock(128, 2, dropout=0.1).train()(torch.randn(1, 4, 128))
 
 
@@ -80,3 +80,23 @@ def test_product_does_not_import_oracle():
     for f in os.listdir(pkg):
         if f.endswith(".py"):
             assert "oracle" not in open(os.path.join(pkg, f)).read(), f
+
+
+def test_dropout_mask_restatement_statistics():
+    """tests/dropout_ref.py (numpy restatement of csrc/gxa_rng.cuh): drop rate, independence, seed sensitivity."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    import numpy as np
+    import dropout_ref as DR
+    m = DR.multipliers(512, 751, 0.1, 0x1234ABCD5678EF01, DR.STREAM_ATTN)
+    keep = m > 0
+    assert set(np.unique(m)) == {np.float32(0.0), np.float32(1.0) / (np.float32(1.0) - np.float32(0.1))}
+    assert abs(keep.mean() - 0.9) < 2e-3
+    assert abs(np.corrcoef(keep[:, :-1].ravel(), keep[:, 1:].ravel())[0, 1]) < 5e-3      # neighbouring keys
+    assert abs(np.corrcoef(keep[:-1].ravel(), keep[1:].ravel())[0, 1]) < 5e-3            # neighbouring rows
+    m2 = DR.multipliers(512, 751, 0.1, 0x1234ABCD5678EF02, DR.STREAM_ATTN)
+    assert abs(np.corrcoef(keep.ravel(), (m2 > 0).ravel())[0, 1]) < 5e-3                 # another seed
+    m3 = DR.multipliers(512, 751, 0.1, 0x1234ABCD5678EF01, DR.STREAM_FFN)
+    assert abs(np.corrcoef(keep.ravel(), (m3 > 0).ravel())[0, 1]) < 5e-3                 # another stream
+    assert np.all(DR.multipliers(4, 9, 0.0, 1, 1) == 1)
