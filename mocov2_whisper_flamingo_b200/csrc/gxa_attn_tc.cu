@@ -109,20 +109,19 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (nblk > 0) {
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);
-      const uint32_t q_base = smem_u32(sm.q), p_base = smem_u32(sm.p), v_base = smem_u32(sm.v);
+      // converged issue (gxa_ptx.cuh): warp-uniform descriptors in all lanes, tcgen05 predicated on the elected lane
+      constexpr uint32_t HI = umma_desc_hi(1024);
+      const uint32_t el = elect_one_pred();
+      const uint32_t qd = umma_desc_lo(smem_u32(sm.q), 16), pd = umma_desc_lo(smem_u32(sm.p), 16);
+      const uint32_t vd = umma_desc_lo(smem_u32(sm.v), 8192);
       auto issue_s = [&](int j) {
         mbar_wait(&sm.k_full[j & 1], (j >> 1) & 1);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t k_base = smem_u32(sm.k[j & 1]);
+        const uint32_t kd = umma_desc_lo(smem_u32(sm.k[j & 1]), 16);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_bf16(tmem_s, umma_desc_sw128(q_base + k * 32, 16, 1024), umma_desc_sw128(k_base + k * 32, 16, 1024),
-                      idesc_s, k > 0 ? 1u : 0u);
-          umma_commit(&sm.s_full);
-          umma_commit(&sm.k_empty[j & 1]);
-        }
-        __syncwarp();
+        for (int k = 0; k < 4; ++k) umma_bf16_e(tmem_s, qd + k * 2, HI, kd + k * 2, HI, idesc_s, k > 0 ? 1u : 0u, el);
+        umma_commit_e(&sm.s_full, el);
+        umma_commit_e(&sm.k_empty[j & 1], el);
       };
       mbar_wait(&sm.q_full, 0);
       issue_s(0);
@@ -134,15 +133,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_wait(&sm.p_ready, j & 1);
         mbar_wait(&sm.v_full, j & 1);
         tc_fence_after();
-        if (lane == 0) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            umma_bf16(tmem_o, umma_desc_sw128(p_base + (k >> 2) * TC_TILE + (k & 3) * 32, 16, 1024),
-                      umma_desc_sw128(v_base + k * 2048, 8192, 1024), idesc_pv, k > 0 ? 1u : 0u);
-          umma_commit(&sm.pv_done);
-          umma_commit(&sm.v_empty);
-        }
-        __syncwarp();
+        for (int k = 0; k < 8; ++k)
+          umma_bf16_e(tmem_o, pd + (k >> 2) * (TC_TILE >> 4) + (k & 3) * 2, HI, vd + k * 128, HI, idesc_pv, k > 0 ? 1u : 0u,
+                      el);
+        umma_commit_e(&sm.pv_done, el);
+        umma_commit_e(&sm.v_empty, el);
       }
     }
   } else {
