@@ -74,7 +74,11 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                     const int* __restrict__ kv_end, const float* __restrict__ lse, const float* __restrict__ delta,
                     float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dk, __nv_bfloat16* __restrict__ dv, int lddkv,
                     int B, int H, int Lq, int Lk, int D, int LqPad, const DropCfg drop, long long* dbg) {
+#ifdef GXA_BWD_STAMPS   // clock stamps of the pipeline events of CTA 0 (tools/dbg_attn_bwd.py); off in the product build
 #define STAMP(role, k) do { if (dbg && blockIdx.x == 0 && g < 16 && lane == 0) dbg[(role) * 128 + g * 8 + (k)] = clock64(); } while (0)
+#else
+#define STAMP(role, k) do { } while (0)
+#endif
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
   if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
