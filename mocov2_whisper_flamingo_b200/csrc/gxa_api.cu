@@ -366,10 +366,10 @@ int gxa_block_prepare_weights(const gxa_dims* d, const gxa_block_params* p, void
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const size_t DD = size_t(d->D) * d->D;
   bf16* w = reinterpret_cast<bf16*>(wcache);
-  GXA_TRY(cast_f32_bf16(p->in_proj_w, w, 3 * DD, s));
-  GXA_TRY(cast_f32_bf16(p->out_proj_w, w + 3 * DD, DD, s));
-  GXA_TRY(cast_f32_bf16(p->ff0_w, w + 4 * DD, 4 * DD, s));
-  GXA_TRY(cast_f32_bf16(p->ff2_w, w + 8 * DD, 4 * DD, s));
+  const float* src[4] = {p->in_proj_w, p->out_proj_w, p->ff0_w, p->ff2_w};
+  void* dst[4] = {w, w + 3 * DD, w + 4 * DD, w + 8 * DD};
+  const size_t n[4] = {3 * DD, DD, 4 * DD, 4 * DD};
+  GXA_TRY(cast_f32_bf16_multi(src, dst, n, 4, s));      // one launch for the layer's four weight matrices
   return 0;
 }
 

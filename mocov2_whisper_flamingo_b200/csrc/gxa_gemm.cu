@@ -188,6 +188,21 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t ou
 }
 
 
+// 2-D fp32 tensor map (output side: TMA reduce-add of 128B-swizzled boxes)
+int make_tmap_f32_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                     uint32_t box_outer) {
+  if (int e = get_encode()) return e;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld * 4) % 16) return GXA_ERR_ALIGN;
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 4};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : GXA_ERR_TMAP;
+}
+
 // 3-D bf16 tensor map [d2][d1][d0] (d0 contiguous): box {b0, b1, 1}, 128B swizzle, OOB rows read as zero.
 int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t ld1,
                       uint64_t ld2, uint32_t b0, uint32_t b1) {

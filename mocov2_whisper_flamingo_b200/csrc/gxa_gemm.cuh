@@ -254,14 +254,34 @@ __device__ __forceinline__ void aux_prefetch(const GemmParams& p, int row0, int 
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* stage, int row0, int col,
                                                   const uint32_t (&r)[32], float gate_t, bool first_split, int lane,
-                                                  const AuxRegs<EPI>& ax) {
+                                                  const AuxRegs<EPI>& ax, const CUtensorMap* tmC = nullptr) {
   const uint32_t sbase = smem_u32(stage);
+  if constexpr (EPI == EPI_F32) {
+    // the previous chunk's TMA reduction must have finished READING this staging buffer
+    if (tmC != nullptr) {
+      if (lane == 0) bulk_wait_group_read0();
+      __syncwarp();
+    }
+  }
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const uint32_t a = sbase + lane * 128 + ((j ^ (lane & 7)) << 4);
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(r[4 * j]), "r"(r[4 * j + 1]),
                  "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
                  : "memory");
+  }
+  if constexpr (EPI == EPI_F32) {
+    // wgrad / split-K accumulation: the staging buffer IS a 128B-swizzled [32 x 32] fp32 box -> one TMA reduce-add
+    // (no LSU atomics; rows past M are clipped by the tensor map)
+    if (tmC != nullptr) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_reduce_add_2d(tmC, stage, col, row0);
+        bulk_commit_group();
+      }
+      return;
+    }
   }
   __syncwarp();
   const int cl = lane & 7, rsub = lane >> 3;

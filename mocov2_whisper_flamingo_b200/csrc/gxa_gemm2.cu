@@ -26,7 +26,8 @@ constexpr int G2_TMEM_COLS = 512;
 
 template <int EPI, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, const GemmParams p, const int tma_c) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* epi_stage = smem + G2_STAGES * G2_STAGE_BYTES;
@@ -185,7 +186,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * G2_BN + half * (G2_BN / 2) + ci * 32, r);
           tmem_ld_wait();
-          epilogue_chunk_v2<EPI>(p, stage_buf, row0, col, r, gate_t, split == 0, lane, ax[ci & 1]);
+          epilogue_chunk_v2<EPI>(p, stage_buf, row0, col, r, gate_t, split == 0, lane, ax[ci & 1], tma_c ? &tmC : nullptr);
         }
       }
       tc_fence_before();
@@ -194,6 +195,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       as ^= 1;
       if (as == 0) aphase ^= 1;
     }
+    if (tma_c && lane == 0) bulk_wait_group0();     // reductions complete before the CTA retires its shared memory
   }
 
   tc_fence_before();
@@ -208,6 +210,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 // ------------------------------------------------------------------ host side
 int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
                    uint32_t box_outer);
+int make_tmap_f32_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                     uint32_t box_outer);
 
 template <int EPI, bool A_MN, bool B_MN>
 static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stream) {
@@ -219,6 +223,12 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   if (!B_MN) e = make_tmap_bf16(&tmB, op.B, op.K, op.N, op.ldb, GEMM_BK, 128);
   else       e = make_tmap_bf16(&tmB, op.B, op.N, op.K, op.ldb, 64, GEMM_BK);
   if (e) return e;
+  // fp32 accumulation (wgrad, split-K, dxa) without a bias goes out as TMA reduce-adds of 32 x 32 boxes
+  CUtensorMap tmC = tmA;
+  int tma_c = 0;
+  if (EPI == EPI_F32 && (p.accumulate || p.k_splits > 1) && p.bias == nullptr &&
+      make_tmap_f32_2d(&tmC, p.C, p.N, p.M, p.ldc, 32, 32) == 0)
+    tma_c = 1;
   auto kern = gemm_tc2_kernel<EPI, A_MN, B_MN>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -230,7 +240,7 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   const int total = num_m * num_n * p.k_splits;
   const int max_pairs = num_sms() / 2;
   const int pairs = total < max_pairs ? total : max_pairs;
-  kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(tmA, tmB, p);
+  kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(tmA, tmB, tmC, p, tma_c);
   count_launch();
   return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }

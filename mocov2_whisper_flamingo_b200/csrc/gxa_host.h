@@ -55,6 +55,7 @@ int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, fl
 int gate_finish(const float* gate, const float* accum, float* dgate, cudaStream_t s);   // dgate = (1-tanh^2) * accum
 int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, cudaStream_t s);   // dst += colsum
 int cast_f32_bf16(const float* src, void* dst, size_t n, cudaStream_t s);
+int cast_f32_bf16_multi(const float* const* src, void* const* dst, const size_t* n, int count, cudaStream_t s);   // <= 4
 int cast_bf16_f32(const void* src, float* dst, size_t n, cudaStream_t s);
 // fp32 -> bf16 hi/lo split for the 3xbf16 fp32-accurate GEMM mode.  pattern 0: [hi|lo|hi], 1: [hi|hi|lo].
 // along_rows = 0: dst is [rows, 3*cols] (segments side by side); 1: dst is [3*rows, cols] (segments stacked).

@@ -236,6 +236,13 @@ __device__ __forceinline__ void bulk_reduce_add_f32(float* gdst, const void* sme
                ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes)
                : "memory");
 }
+// fp32 reduce-add of a 128B-swizzled smem box into a 2-D global tensor (TMA engine; rows / columns outside the tensor
+// are clipped by the hardware)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_group0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }

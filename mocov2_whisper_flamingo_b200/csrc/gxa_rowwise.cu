@@ -480,6 +480,42 @@ static inline int ew_grid(size_t n4) {
   size_t cap = size_t(num_sms()) * 8;
   return int(b < cap ? (b ? b : 1) : cap);
 }
+// up to 4 independent (src, dst, n) segments in ONE launch: the per-layer weight re-cast of every training step
+struct CastSegs {
+  const float* src[4];
+  __nv_bfloat16* dst[4];
+  size_t end4[4];          // cumulative float4 counts
+};
+__global__ void cast_segs_kernel(const CastSegs segs) {
+  const size_t total = segs.end4[3];
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    int k = 0;
+    size_t base = 0;
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      if (i >= segs.end4[j]) { k = j + 1; base = segs.end4[j]; }
+    const size_t o = 4 * (i - base);
+    st4_bf16(segs.dst[k] + o, ld4(segs.src[k] + o));
+  }
+}
+int cast_f32_bf16_multi(const float* const* src, void* const* dst, const size_t* n, int count, cudaStream_t s) {
+  if (count < 1 || count > 4) return GXA_ERR_ARG;
+  CastSegs segs;
+  size_t acc = 0;
+  for (int j = 0; j < 4; ++j) {
+    const int jj = j < count ? j : count - 1;
+    if (j < count) {
+      if (n[j] % 4) return GXA_ERR_SHAPE;
+      acc += n[j] / 4;
+    }
+    segs.src[j] = src[jj];
+    segs.dst[j] = reinterpret_cast<__nv_bfloat16*>(dst[jj]);
+    segs.end4[j] = acc;
+  }
+  if (acc == 0) return 0;
+  cast_segs_kernel<<<ew_grid(acc), 256, 0, s>>>(segs);
+  return check_launch();
+}
 int cast_f32_bf16(const float* src, void* dst, size_t n, cudaStream_t s) {
   if (n % 4) return GXA_ERR_SHAPE;
   if (n == 0) return 0;
