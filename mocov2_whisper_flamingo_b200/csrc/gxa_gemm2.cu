@@ -6,9 +6,9 @@
 // tensor cores of both SMs consume both halves, so per-SM smem traffic drops by a third and L2->SM traffic
 // per FLOP drops from 1/85 to 1/128 B/FLOP.
 //
-//   warp 8 (both CTAs)  : TMA producer for its CTA's A rows / B half; bytes complete on the LEADER's barrier
-//   warp 9 (leader only): issues tcgen05.mma.cta_group::2, commits multicast to both CTAs' barriers
-//   warps 0-7 (both)    : epilogue of the CTA's own 128 x 256 accumulator (TMEM -> smem transpose -> coalesced HBM)
+//   warp 16 (both CTAs) : TMA producer for its CTA's A rows / B half; bytes complete on the LEADER's barrier
+//   warp 17 (leader only): issues tcgen05.mma.cta_group::2, commits multicast to both CTAs' barriers
+//   warps 0-15 (both)   : epilogue of the CTA's own 128 x 256 accumulator (TMEM -> smem transpose -> coalesced HBM)
 #include "gxa_gemm.cuh"
 #include "gxa_host.h"
 
@@ -16,18 +16,29 @@ namespace gxa {
 
 constexpr int G2_BM = 256;        // per pair
 constexpr int G2_BN = 256;
-constexpr int G2_STAGES = 6;
 constexpr int G2_A_BYTES = 128 * GEMM_BK * 2;      // this CTA's 128 rows of A
 constexpr int G2_B_BYTES = 128 * GEMM_BK * 2;      // this CTA's 128 columns of B
 constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_B_BYTES;
-constexpr int G2_EPI_STAGE_BYTES = GEMM_EPI_WARPS * 4096;
-constexpr int G2_SMEM_BYTES = G2_STAGES * G2_STAGE_BYTES + G2_EPI_STAGE_BYTES + 1024 + 256;
+// Epilogue width per fused epilogue: the GELU epilogues are latency-bound with 2 warps per scheduler (ncu: < 50 % issue
+// utilisation), so they get 16 epilogue warps (4 per TMEM lane quarter, 64 accumulator columns each) and give one smem
+// stage to the extra staging buffers; the others keep 8 warps and the 6-stage ring (long-K wgrad wants the depth).
+template <int EPI>
+struct G2Cfg {
+  static constexpr int EPI_WARPS = (EPI == EPI_BIAS_GELU || EPI == EPI_GELU_BWD) ? 16 : 8;
+  static constexpr int THREADS = (EPI_WARPS + 2) * 32;
+  static constexpr int COLS_PER_WARP = 256 / (EPI_WARPS / 4);
+  static constexpr int STAGES = EPI_WARPS == 16 ? 5 : 6;
+  static constexpr int EPI_STAGE_BYTES = EPI_WARPS * 4096;
+  static constexpr int SMEM_BYTES = STAGES * G2_STAGE_BYTES + EPI_STAGE_BYTES + 1024 + 256;
+};
 constexpr int G2_TMEM_COLS = 512;
 
 template <int EPI, bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G2Cfg<EPI>::THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmC, const GemmParams p, const int tma_c) {
+  constexpr int G2_EPI_WARPS = G2Cfg<EPI>::EPI_WARPS, G2_STAGES = G2Cfg<EPI>::STAGES;
+  constexpr int G2_COLS_PER_WARP = G2Cfg<EPI>::COLS_PER_WARP, G2_EPI_STAGE_BYTES = G2Cfg<EPI>::EPI_STAGE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* epi_stage = smem + G2_STAGES * G2_STAGE_BYTES;
@@ -58,21 +69,21 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 2 * GEMM_EPI_WARPS);
+      mbar_init(&tempty[i], 2 * G2_EPI_WARPS);
     }
     mbar_fence_init();
   }
-  if (warp == 8 && lane == 0) {
+  if (warp == G2_EPI_WARPS && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
-  if (warp == 9) tmem_alloc_pair(tmem_slot, G2_TMEM_COLS);
+  if (warp == G2_EPI_WARPS + 1) tmem_alloc_pair(tmem_slot, G2_TMEM_COLS);
   tc_fence_before();
   cluster_sync_all();                 // barrier inits + TMEM allocation visible in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 8) {
+  if (warp == G2_EPI_WARPS) {
     // ------------------------------------------------------------ TMA producer (both CTAs)
     if (lane == 0) {
       int stage = 0;
@@ -105,7 +116,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == G2_EPI_WARPS + 1) {
     // ------------------------------------------------------------ MMA issuer (leader CTA only)
     if (leader) {
       constexpr uint32_t idesc = umma_idesc_bf16(G2_BM, G2_BN, A_MN, B_MN);
@@ -146,7 +157,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else {
     // ------------------------------------------------------------ epilogue warps 0..7 (both CTAs)
     const int quarter = warp & 3;
-    const int half = warp >> 2;
+    const int half = warp >> 2;          // column group of this warp: G2_COLS_PER_WARP accumulator columns
     uint8_t* stage_buf = epi_stage + warp * 4096;
     float gate_t = 0.f;
     if constexpr (EPI == EPI_GATE_RES) gate_t = tanhf(__ldg(p.gate));
@@ -154,12 +165,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t tempty_leader1 = mapa_shared(smem_u32(&tempty[1]), 0);
     int as = 0;
     uint32_t aphase = 0;
-    constexpr int CHUNKS = G2_BN / 2 / 32;           // 32-column chunks per warp per tile
+    constexpr int CHUNKS = G2_COLS_PER_WARP / 32;           // 32-column chunks per warp per tile
     AuxRegs<EPI> ax[2];                              // chunk operands from HBM, fetched one chunk ahead
     auto tile_origin = [&](int w, int& row0, int& n0) {
       const int tile = w / p.k_splits;
       row0 = (tile / num_n) * G2_BM + rank * 128 + quarter * 32;
-      n0 = (tile % num_n) * G2_BN + half * (G2_BN / 2);
+      n0 = (tile % num_n) * G2_BN + half * G2_COLS_PER_WARP;
     };
     if (pair < total) {
       int r0, n0;
@@ -184,7 +195,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         if (col < p.N) {
           uint32_t r[32];
-          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * G2_BN + half * (G2_BN / 2) + ci * 32, r);
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * G2_BN + half * G2_COLS_PER_WARP + ci * 32, r);
           tmem_ld_wait();
           epilogue_chunk_v2<EPI>(p, stage_buf, row0, col, r, gate_t, split == 0, lane, ax[ci & 1], tma_c ? &tmC : nullptr);
         }
@@ -201,7 +212,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   tc_fence_before();
   __syncwarp();
   cluster_sync_all();                 // nobody exits (or frees TMEM) while the peer may still signal / read
-  if (warp == 9) {
+  if (warp == G2_EPI_WARPS + 1) {
     tc_fence_after();
     tmem_dealloc_pair(tmem_base, G2_TMEM_COLS);
   }
@@ -232,7 +243,7 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   auto kern = gemm_tc2_kernel<EPI, A_MN, B_MN>;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES) != cudaSuccess)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<EPI>::SMEM_BYTES) != cudaSuccess)
       return GXA_ERR_CUDA;
     attr_set = true;
   }
@@ -240,7 +251,7 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   const int total = num_m * num_n * p.k_splits;
   const int max_pairs = num_sms() / 2;
   const int pairs = total < max_pairs ? total : max_pairs;
-  kern<<<2 * pairs, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(tmA, tmB, tmC, p, tma_c);
+  kern<<<2 * pairs, G2Cfg<EPI>::THREADS, G2Cfg<EPI>::SMEM_BYTES, stream>>>(tmA, tmB, tmC, p, tma_c);
   count_launch();
   return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }
