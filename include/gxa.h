@@ -115,6 +115,19 @@ int gxa_block_bwd(const gxa_dims* d, const gxa_block_params* p, const void* wcac
                   const uint8_t* mask, const int32_t* kv_end, const void* saved, const float* dy, float* dx, float* dxa,
                   const gxa_block_grads* g, void* workspace, void* stream);
 
+/* ---- decode-time path (the reference has no decode loop -- this must equal the block's forward on the
+ * same query rows).  The visual memory xa is fixed during decoding, so K|V = xa [Wk;Wv]^T + b are projected ONCE per
+ * layer into a bf16 cache [B*Lk, 2D]; each step runs the block on the new query rows only (x: fp32 [B*Lq, D], usually
+ * Lq = 1, or Lq = beams: the beams of a sample share its cache and the block has no interaction between query
+ * positions).  bf16 precision, no dropout, nothing saved for backward. */
+size_t gxa_block_kv_cache_bytes(const gxa_dims* d);
+int gxa_block_kv_prefill(const gxa_dims* d, const gxa_block_params* p, const void* wcache, const void* xa_op,
+                         void* kv_cache, void* stream);
+size_t gxa_block_decode_workspace_bytes(const gxa_dims* d);
+int gxa_block_decode(const gxa_dims* d, const gxa_block_params* p, const void* wcache, const float* x,
+                     const void* kv_cache, const uint8_t* mask, const int32_t* kv_end, float* y, void* workspace,
+                     void* stream);
+
 /* ---- building blocks, exported for unit parity tests and for the stack driver ---------- */
 /* LayerNorm.forward (gate_cross_attention.py:8-10): fp32 statistics, eps 1e-5. out fp32 or bf16. */
 int gxa_layernorm_fwd(const float* x, const float* w, const float* b, void* out, int out_is_f32, float* mean,

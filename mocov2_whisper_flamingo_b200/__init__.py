@@ -6,7 +6,8 @@ Everything below them is hand-written CUDA behind the C ABI in include/gxa.h.
 """
 from .gate_cross_attention import (GatedCrossAttentionBlock, GatedCrossModalFusion, LayerNorm,  # noqa: F401
                                    set_default_precision)
+from .decode import DecodeState  # noqa: F401
 from ._lib import LIB_PATH, launch_count  # noqa: F401
 
 __all__ = ["LayerNorm", "GatedCrossAttentionBlock", "GatedCrossModalFusion", "set_default_precision",
-           "launch_count", "LIB_PATH"]
+           "DecodeState", "launch_count", "LIB_PATH"]

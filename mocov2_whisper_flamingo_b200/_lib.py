@@ -48,6 +48,10 @@ SIGNATURES = {
     "gxa_xa_prepare": (_i, [_dp, _vp, _vp, _vp]),
     "gxa_block_fwd": (_i, [_dp, _bp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gxa_block_bwd": (_i, [_dp, _bp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _bp, _vp, _vp]),
+    "gxa_block_kv_cache_bytes": (_sz, [_dp]),
+    "gxa_block_kv_prefill": (_i, [_dp, _bp, _vp, _vp, _vp, _vp]),
+    "gxa_block_decode_workspace_bytes": (_sz, [_dp]),
+    "gxa_block_decode": (_i, [_dp, _bp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gxa_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp]),
     "gxa_layernorm_bwd": (_i, [_vp] * 9 + [_i, _i, _vp]),
     "gxa_linear_workspace_bytes": (_sz, [_i, _i, _i, _i]),

@@ -173,17 +173,21 @@ struct WCache {
 // ================================================================== forward
 static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const void* wcache, const float* x,
                           const void* xa_op, const uint8_t* mask, const int32_t* kv_end, float* y, void* saved,
-                          cudaStream_t s) {
+                          cudaStream_t s, const bf16* kv_cached = nullptr) {
   const int M = d.B * d.Lq, Mk = d.B * d.Lk, D = d.D;
-  SavedBf16 S(d, saved);
+  gxa_dims dc = d;
+  if (kv_cached != nullptr) dc.Lk = 1;     // decode: the activation carve has no K|V slot of its own ...
+  SavedBf16 S(dc, saved);
   WCache W(d, wcache);
+  if (kv_cached != nullptr) S.kv = const_cast<bf16*>(kv_cached);   // ... K|V were projected once (gxa_block_kv_prefill)
   const float* x1 = x;
   if (d.has_xa) {
     GXA_TRY(ln_fwd(x, p.attn_ln_w, p.attn_ln_b, S.h, 0, S.mean1, S.rstd1, M, D, s));
     GXA_TRY(gemm_bf16(S.h, D, false, W.in_proj, D, false, M, D, D, EPI_BF16, S.q, D, nullptr, 0, p.in_proj_b, nullptr, 0,
                       nullptr, 0, s));
-    GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, S.kv, 2 * D, nullptr,
-                      0, p.in_proj_b + D, nullptr, 0, nullptr, 0, s));
+    if (kv_cached == nullptr)
+      GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, S.kv, 2 * D,
+                        nullptr, 0, p.in_proj_b + D, nullptr, 0, nullptr, 0, s));
     GXA_TRY(attn_fwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, D, S.lse, d.B, d.H, d.Lq, d.Lk, s,
                           make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
     GXA_TRY(gemm_bf16(S.ctx, D, false, W.out, D, false, M, D, D, EPI_GATE_RES, S.x1, D, S.o, D, p.out_proj_b, x, D,
@@ -404,6 +408,40 @@ int gxa_block_fwd(const gxa_dims* d, const gxa_block_params* p, const void* wcac
   }
   if (!workspace) return GXA_ERR_ARG;
   return block_fwd_f32(*d, *p, x, xa_op, mask, y, saved, workspace, s);
+}
+
+// ---- decode-time path: K|V of the (fixed) visual memory are projected once per layer and cached;
+// every decoding step then runs the block on the new query rows only.  Beams of one sample share its cache: pass them
+// as the Lq dimension (the block has no interaction between query positions).
+size_t gxa_block_kv_cache_bytes(const gxa_dims* d) {
+  if (check_dims(d) || !d->has_xa) return 0;
+  return size_t(d->B) * d->Lk * 2 * d->D * sizeof(bf16);
+}
+int gxa_block_kv_prefill(const gxa_dims* d, const gxa_block_params* p, const void* wcache, const void* xa_op,
+                         void* kv_cache, void* stream) {
+  GXA_TRY(check_dims(d));
+  if (!p || !wcache || !xa_op || !kv_cache || !d->has_xa) return GXA_ERR_ARG;
+  if (d->precision != GXA_PREC_BF16) return GXA_ERR_UNSUPPORTED;
+  const int Mk = d->B * d->Lk, D = d->D;
+  WCache W(*d, wcache);
+  GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, kv_cache, 2 * D, nullptr,
+                    0, p->in_proj_b + D, nullptr, 0, nullptr, 0, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+size_t gxa_block_decode_workspace_bytes(const gxa_dims* d) {
+  if (check_dims(d)) return 0;
+  gxa_dims q = *d;
+  q.Lk = 1;                               // the K|V slot of the activation carve is not used (external cache)
+  return SavedBf16(q, nullptr).bytes;
+}
+int gxa_block_decode(const gxa_dims* d, const gxa_block_params* p, const void* wcache, const float* x,
+                     const void* kv_cache, const uint8_t* mask, const int32_t* kv_end, float* y, void* workspace,
+                     void* stream) {
+  GXA_TRY(check_dims(d));
+  if (!p || !wcache || !x || !y || x == y || !workspace || !kv_cache || !d->has_xa) return GXA_ERR_ARG;
+  if (d->precision != GXA_PREC_BF16 || d->p_drop != 0.f) return GXA_ERR_UNSUPPORTED;   // inference: bf16, no dropout
+  return block_fwd_bf16(*d, *p, wcache, x, nullptr, mask, kv_end, y, workspace, reinterpret_cast<cudaStream_t>(stream),
+                        reinterpret_cast<const bf16*>(kv_cache));
 }
 
 int gxa_block_bwd(const gxa_dims* d, const gxa_block_params* p, const void* wcache, const float* x, const void* xa_op,
