@@ -19,7 +19,7 @@ LIB = os.path.join(HERE, "libgxa_b200.so")
 SOURCES = ["gxa_gemm.cu", "gxa_gemm2.cu", "gxa_rowwise.cu", "gxa_attn.cu", "gxa_attn_tc.cu", "gxa_attn_bwd_tc.cu", "gxa_attn_f32.cu", "gxa_api.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC"]
+         "-Xcompiler", "-fPIC"] + os.environ.get("GXA_NVCC_EXTRA", "").split()     # e.g. -DGXA_BWD_STAMPS (tools/)
 
 
 def _deps_mtime() -> float:
