@@ -221,6 +221,8 @@ attn_fwd_kernel(const __nv_bfloat16* __restrict__ q, int ldq, const __nv_bfloat1
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ ctx, const __nv_bfloat16* __restrict__ dctx, int ldc,
                   float* __restrict__ delta, int B, int H, int Lq) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int l = threadIdx.x & 31;
   if (row >= B * Lq) return;
@@ -462,8 +464,8 @@ int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
   auto K = reinterpret_cast<const __nv_bfloat16*>(k);
   auto V = reinterpret_cast<const __nv_bfloat16*>(v);
   auto dO = reinterpret_cast<const __nv_bfloat16*>(dctx);
-  attn_delta_kernel<<<(B * Lq + 7) / 8, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(ctx), dO, ldc, delta, B, H,
-                                                     Lq);
+  launch_pdl(attn_delta_kernel, dim3((B * Lq + 7) / 8), dim3(256), 0, s, reinterpret_cast<const __nv_bfloat16*>(ctx), dO, ldc,
+             delta, B, H, Lq);
   if (int e = chk()) return e;
   // tcgen05 path: K|V (and dK|dV) packed side by side, scratch for the fp32 dQ accumulator available
   const bool packed = workspace != nullptr && ldkv == 2 * H * 64 && lddkv == ldkv && V == K + H * 64 &&

@@ -111,6 +111,7 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); tma_prefetch_desc(&tmDO);
   }
   if (warp == COMPUTE_WARPS + DRAIN_WARPS + 1) tmem_alloc(&sm.tmem_slot, 512);
+  pdl_wait();                           // everything below reads / writes global memory
   for (int t = threadIdx.x; t < MAX_ITEMS; t += THREADS) {
     const int w = blockIdx.x + t * gridDim.x;
     uint8_t lv = 0;
@@ -161,6 +162,7 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         w = w2;
         cur = nxt;
       }
+      pdl_launch_dependents();                   // all loads of this CTA issued: the next kernel may be staged
     }
   } else if (warp == COMPUTE_WARPS + DRAIN_WARPS + 1) {
     // ------------------------------------------------------------ MMA issuer
@@ -294,16 +296,25 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (warp == 0) STAMP(1, 6);
         float pv[32], dsv[32];
         const float nls = -ls * kLog2e;
-        if (!any_masked) {
+        // packed f32x2 arithmetic (FFMA2 / FMUL2 / FADD2): half the issue slots of the scalar forms; the compute warps'
+        // instruction stream is on the critical path of every iteration
+        const float2 c2 = make_float2(kScaleLog2, kScaleLog2), nls2 = make_float2(nls, nls), nde2 = make_float2(-de, -de);
 #pragma unroll
-          for (int c = 0; c < 32; ++c) pv[c] = ex2a(fmaf(__uint_as_float(sr[c]), kScaleLog2, nls));
-        } else {
-#pragma unroll
-          for (int c = 0; c < 32; ++c) pv[c] = ex2a(fmaf(__uint_as_float(sr[c]) + kbias[c], kScaleLog2, nls));
+        for (int c = 0; c < 16; ++c) {
+          float2 sv = make_float2(__uint_as_float(sr[2 * c]), __uint_as_float(sr[2 * c + 1]));
+          if (any_masked) sv = __fadd2_rn(sv, *reinterpret_cast<const float2*>(kbias + 2 * c));
+          const float2 e = __ffma2_rn(sv, c2, nls2);
+          pv[2 * c] = ex2a(e.x);
+          pv[2 * c + 1] = ex2a(e.y);
         }
         if (drop.thresh == 0) {
 #pragma unroll
-          for (int c = 0; c < 32; ++c) dsv[c] = pv[c] * (__uint_as_float(dr[c]) - de);
+          for (int c = 0; c < 16; ++c) {
+            const float2 d = __fadd2_rn(make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1])), nde2);
+            const float2 t = __fmul2_rn(make_float2(pv[2 * c], pv[2 * c + 1]), d);
+            dsv[2 * c] = t.x;
+            dsv[2 * c + 1] = t.y;
+          }
         } else {
           // dropout on the probabilities (forward: ctx = (m*P) V): dV sees m*P, dP = m * (dO V^T); same mask as forward
           const uint32_t ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) *
@@ -313,11 +324,14 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             bool k0, k1;
             drop_keep(drop, ctr + c, k0, k1);
             // dS = P*(m*dP - delta) = (m*P)*dP - P*delta ;  the P tile for dV holds m*P
-            const float t0 = pv[2 * c] * de, t1 = pv[2 * c + 1] * de;
-            pv[2 * c] = k0 ? pv[2 * c] * drop.scale : 0.f;
-            pv[2 * c + 1] = k1 ? pv[2 * c + 1] * drop.scale : 0.f;
-            dsv[2 * c] = fmaf(pv[2 * c], __uint_as_float(dr[2 * c]), -t0);
-            dsv[2 * c + 1] = fmaf(pv[2 * c + 1], __uint_as_float(dr[2 * c + 1]), -t1);
+            const float2 p0 = make_float2(pv[2 * c], pv[2 * c + 1]);
+            const float2 t = __fmul2_rn(p0, nde2);
+            const float2 pm = __fmul2_rn(p0, make_float2(k0 ? drop.scale : 0.f, k1 ? drop.scale : 0.f));
+            const float2 d = __ffma2_rn(pm, make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1])), t);
+            pv[2 * c] = pm.x;
+            pv[2 * c + 1] = pm.y;
+            dsv[2 * c] = d.x;
+            dsv[2 * c + 1] = d.y;
           }
         }
         if (warp == 0) STAMP(1, 2);
@@ -486,6 +500,8 @@ __global__ void __launch_bounds__(256)
 attn_dq_finalize2_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dq, int lddq, int H, int Lq, int nq,
                          float* __restrict__ dq_colsum) {
   __shared__ float4 tile[16][BQ + 1];
+  pdl_launch_dependents();
+  pdl_wait();
   const int blk = blockIdx.x;                       // (b*H + h)*nq + i
   const int i = blk % nq, bh = blk / nq, h = bh % H, b = bh / H;
   const float4* src = reinterpret_cast<const float4*>(acc) + size_t(blk) * 16 * BQ;
@@ -539,16 +555,16 @@ int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t
   const int total = B * H * ((Lk + BK - 1) / BK);
   int grid = total < num_sms() ? total : num_sms();
   if ((total + grid - 1) / grid > MAX_ITEMS) grid = (total + MAX_ITEMS - 1) / MAX_ITEMS;
-  attn_bwd_tc2_kernel<<<grid, THREADS, SMEM_BYTES, s>>>(tmQ, tmKV, tmDO, mask, kv_end, lse, delta, dq_acc,
-                                                        reinterpret_cast<__nv_bfloat16*>(dk),
-                                                        reinterpret_cast<__nv_bfloat16*>(dv), lddkv, B, H, Lq, Lk, D, LqPad, drop,
-                                                        getenv("GXA_DBG_PTR") ? reinterpret_cast<long long*>(strtoull(getenv("GXA_DBG_PTR"), nullptr, 0)) : nullptr);
+  long long* dbg = getenv("GXA_DBG_PTR") ? reinterpret_cast<long long*>(strtoull(getenv("GXA_DBG_PTR"), nullptr, 0)) : nullptr;
+  cudaError_t le = launch_pdl(attn_bwd_tc2_kernel, dim3(grid), dim3(THREADS), SMEM_BYTES, s, tmQ, tmKV, tmDO, mask, kv_end, lse,
+                              delta, dq_acc, reinterpret_cast<__nv_bfloat16*>(dk), reinterpret_cast<__nv_bfloat16*>(dv), lddkv,
+                              B, H, Lq, Lk, D, LqPad, drop, dbg);
   count_launch();
-  if (cudaGetLastError() != cudaSuccess) return GXA_ERR_CUDA;
-  attn_dq_finalize2_kernel<<<B * H * (LqPad / BQ), 256, 0, s>>>(dq_acc, reinterpret_cast<__nv_bfloat16*>(dq), lddq, H, Lq,
-                                                               LqPad / BQ, dq_colsum);
+  if (le != cudaSuccess || cudaGetLastError() != cudaSuccess) return GXA_ERR_CUDA;
+  le = launch_pdl(attn_dq_finalize2_kernel, dim3(B * H * (LqPad / BQ)), dim3(256), 0, s, dq_acc,
+                  reinterpret_cast<__nv_bfloat16*>(dq), lddq, H, Lq, LqPad / BQ, dq_colsum);
   count_launch();
-  return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
+  return le == cudaSuccess && cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }
 
 }  // namespace gxa

@@ -316,8 +316,6 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * TC_BQ, h = blockIdx.y, b = blockIdx.z;
-  const int kend = kv_end ? min(kv_end[b], Lk) : Lk;
-  const int nblk = (kend + TC_BK - 1) / TC_BK;
 
   if (threadIdx.x == 0) {
     mbar_init(&sm.q_full, 1);
@@ -333,6 +331,9 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == TC_SOFTMAX_WARPS && lane == 0) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); }
   if (warp == TC_SOFTMAX_WARPS + 1) tmem_alloc(&sm.tmem_slot, 256);
   __syncthreads();
+  pdl_wait();                           // prologue done; everything below reads / writes global memory
+  const int kend = kv_end ? min(kv_end[b], Lk) : Lk;
+  const int nblk = (kend + TC_BK - 1) / TC_BK;
   {
     const uint8_t* mg = mask ? mask + size_t(b) * Lk : nullptr;
     for (int key = threadIdx.x; key < nblk * TC_BK; key += TC_FWD_THREADS) {
@@ -363,6 +364,7 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tma_load_3d(sm.v[st], &tmKV, &sm.v_full[st], D + h * TC_HD, j * TC_BK, b);
       }
     }
+    if (lane == 0) pdl_launch_dependents();      // all loads of this CTA issued: the next kernel may be staged
   } else if (warp == TC_SOFTMAX_WARPS + 1) {
     // ------------------------------------------------------------ MMA issuer
     if (nblk > 0) {
@@ -421,9 +423,13 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (lane == 0) mbar_arrive(&sm.s_free);
       if (any_masked) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          s0[i] = __float_as_uint(__uint_as_float(s0[i]) + kb[i]);
-          s1[i] = __float_as_uint(__uint_as_float(s1[i]) + kb[32 + i]);
+        for (int i = 0; i < 32; i += 2) {
+          const float2 a = __fadd2_rn(make_float2(__uint_as_float(s0[i]), __uint_as_float(s0[i + 1])),
+                                      *reinterpret_cast<const float2*>(kb + i));
+          const float2 c = __fadd2_rn(make_float2(__uint_as_float(s1[i]), __uint_as_float(s1[i + 1])),
+                                      *reinterpret_cast<const float2*>(kb + 32 + i));
+          s0[i] = __float_as_uint(a.x); s0[i + 1] = __float_as_uint(a.y);
+          s1[i] = __float_as_uint(c.x); s1[i + 1] = __float_as_uint(c.y);
         }
       }
       float mx = -INFINITY, mx2 = -INFINITY;
@@ -461,14 +467,23 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
       const float mneg = -m_use * kScaleLog2_tc + drop_log2;    // dropout: p carries the 1/(1-p) factor
-      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+      float2 la = make_float2(0.f, 0.f), lb = make_float2(0.f, 0.f);
+      const float2 c2 = make_float2(kScaleLog2_tc, kScaleLog2_tc), mneg2 = make_float2(mneg, mneg);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         float pv[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) pv[i] = ex2_approx(fmaf(__uint_as_float(c == 0 ? s0[i] : s1[i]), kScaleLog2_tc, mneg));
+        for (int i = 0; i < 32; i += 2) {      // packed f32x2 FMA for the exponent argument, packed adds for the row sum
+          const float2 e = __ffma2_rn(make_float2(__uint_as_float(c == 0 ? s0[i] : s1[i]),
+                                                  __uint_as_float(c == 0 ? s0[i + 1] : s1[i + 1])), c2, mneg2);
+          pv[i] = ex2_approx(e.x);
+          pv[i + 1] = ex2_approx(e.y);
+        }
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) { l0 += pv[i]; l1 += pv[i + 1]; l2 += pv[i + 2]; l3 += pv[i + 3]; }
+        for (int i = 0; i < 32; i += 4) {
+          la = __fadd2_rn(la, make_float2(pv[i], pv[i + 1]));
+          lb = __fadd2_rn(lb, make_float2(pv[i + 2], pv[i + 3]));
+        }
         if (drop.thresh != 0) {      // the row sum above stays undropped (softmax first); dropping is one select per element
           const uint32_t ctr = drop_row + ((j * TC_BK + half * 64 + c * 32) >> 1);
 #pragma unroll
@@ -484,7 +499,7 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(pv[2 * i], pv[2 * i + 1]);
         tmem_st_32x16(tmem_p + lane_addr + half * 32 + c * 16, pk);
       }
-      l += (l0 + l1) + (l2 + l3);
+      l += (la.x + la.y) + (lb.x + lb.y);
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
@@ -547,8 +562,8 @@ int attn_fwd_tc(const void* q, int ldq, const void* kv, int ldkv, const uint8_t*
     attn_fwd_tc_kernel<<<grid, TC_FWD_THREADS, FWD_TC_SMEM, s>>>(tmQ, tmKV, mask, kv_end, reinterpret_cast<__nv_bfloat16*>(ctx),
                                                                  ldc, lse, H, Lq, Lk, D, drop);
   else
-    attn_fwd_tc2_kernel<<<grid, TC_FWD_THREADS, FWD_TC2_SMEM, s>>>(tmQ, tmKV, mask, kv_end, reinterpret_cast<__nv_bfloat16*>(ctx),
-                                                                   ldc, lse, H, Lq, Lk, D, drop);
+    launch_pdl(attn_fwd_tc2_kernel, grid, dim3(TC_FWD_THREADS), FWD_TC2_SMEM, s, tmQ, tmKV, mask, kv_end,
+               reinterpret_cast<__nv_bfloat16*>(ctx), ldc, lse, H, Lq, Lk, D, drop);
   count_launch();
   return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }

@@ -47,6 +47,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                           // prologue done; everything below reads / writes global memory
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 8) {
@@ -55,6 +56,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        if (w + gridDim.x >= total) pdl_launch_dependents();   // last tile of this CTA: the next kernel may be staged
         const int split = w % p.k_splits;
         const int tile = w / p.k_splits;
         const int m0 = (tile / num_n) * GEMM_BM;
@@ -239,9 +241,9 @@ static int launch_inst(const GemmOp& op, const GemmParams& p, cudaStream_t strea
   const int num_m = (p.M + GEMM_BM - 1) / GEMM_BM, num_n = (p.N + BN - 1) / BN;
   const int total = num_m * num_n * p.k_splits;
   const int grid = total < num_sms() ? total : num_sms();
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, p);
+  const cudaError_t le = launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, p);
   count_launch();
-  return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
+  return le == cudaSuccess && cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }
 
 template <int BN, int EPI>

@@ -81,6 +81,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   tc_fence_before();
   cluster_sync_all();                 // barrier inits + TMEM allocation visible in both CTAs
   tc_fence_after();
+  pdl_wait();                         // prologue done; everything below reads / writes global memory
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == G2_EPI_WARPS) {
@@ -89,6 +90,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int stage = 0;
       uint32_t phase = 0;
       for (int w = pair; w < total; w += num_pairs) {
+        if (w + num_pairs >= total) pdl_launch_dependents();   // last tile of this CTA: the next kernel may be staged
         const int split = w % p.k_splits;
         const int tile = w / p.k_splits;
         const int m0 = (tile / num_n) * G2_BM + rank * 128;
@@ -251,9 +253,10 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   const int total = num_m * num_n * p.k_splits;
   const int max_pairs = num_sms() / 2;
   const int pairs = total < max_pairs ? total : max_pairs;
-  kern<<<2 * pairs, G2Cfg<EPI>::THREADS, G2Cfg<EPI>::SMEM_BYTES, stream>>>(tmA, tmB, tmC, p, tma_c);
+  const cudaError_t le = launch_pdl(kern, dim3(2 * pairs), dim3(G2Cfg<EPI>::THREADS), G2Cfg<EPI>::SMEM_BYTES, stream, tmA, tmB,
+                                    tmC, p, tma_c);
   count_launch();
-  return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
+  return le == cudaSuccess && cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }
 
 template <int EPI>

@@ -18,6 +18,31 @@ typedef CUresult (*PFN_cuTensorMapEncodeTiled_t)(CUtensorMap*, CUtensorMapDataTy
 int num_sms();
 void count_launch();
 
+// Programmatic dependent launch: the kernel may be scheduled while its predecessor on the stream is still running, so
+// its prologue (barrier init, TMEM allocation, tensor-map prefetch) and the launch latency overlap the predecessor's
+// tail.  Every kernel launched through here executes pdl_wait() (gxa_ptx.cuh) before its first global-memory access.
+// GXA_PDL=0 in the environment turns the attribute off (plain stream order) for A/B runs.
+bool pdl_enabled();
+#ifdef __CUDACC__
+// device side: let the next kernel on the stream start its prologue / wait for every earlier kernel's memory
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // C[M,N] = A * B^T with the fused epilogue `epi` (see gxa_gemm.cuh).
 struct GemmOp {
   const void* A = nullptr; int lda = 0; bool a_mn = false;   // a_mn: A stored [K, M] (M contiguous)

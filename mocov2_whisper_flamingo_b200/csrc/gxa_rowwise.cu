@@ -43,6 +43,8 @@ __global__ void __launch_bounds__(RW_WARPS * 32) ln_fwd_kernel(const float* __re
                                                                const float* __restrict__ b, void* __restrict__ out,
                                                                int out_is_f32, float* __restrict__ mean,
                                                                float* __restrict__ rstd, int rows) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int D = 128 * NV;
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * RW_WARPS + (threadIdx.x >> 5);
@@ -99,7 +101,7 @@ int ln_fwd(const float* x, const float* w, const float* b, void* out, int out_is
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
   const int grid = (rows + RW_WARPS - 1) / RW_WARPS;
-  GXA_NV_DISPATCH(D, (ln_fwd_kernel<NV><<<grid, RW_WARPS * 32, 0, s>>>(x, w, b, out, out_is_f32, mean, rstd, rows)));
+  GXA_NV_DISPATCH(D, (launch_pdl(ln_fwd_kernel<NV>, dim3(grid), dim3(RW_WARPS * 32), 0, s, x, w, b, out, out_is_f32, mean, rstd, rows)));
   return check_launch();
 }
 
@@ -205,6 +207,8 @@ ln_bwd_split_kernel(const void* __restrict__ g, int g_is_f32, const float* __res
                     float* __restrict__ dx, float* __restrict__ dw, float* __restrict__ db, const void* __restrict__ o,
                     int o_is_f32, const float* __restrict__ gate, float* __restrict__ dgate_accum, void* __restrict__ dout,
                     float* __restrict__ dbias_out, int rows) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int D = 128 * NVW * W;
   constexpr int GROUPS = RW_WARPS / W;
   extern __shared__ float sm[];                       // [GROUPS][D] column flush
@@ -315,15 +319,15 @@ static int ln_bwd_split_launch(const void* g, int g_is_f32, const float* x, cons
     static int grid_cap = 0;
     if (!grid_cap) grid_cap = resident_grid(k, smem, 1 << 30, GROUPS);
     const int blocks = (rows + GROUPS - 1) / GROUPS;
-    k<<<blocks < grid_cap ? blocks : grid_cap, RW_WARPS * 32, smem, s>>>(g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, o,
-                                                                          o_is_f32, gate, dgate_accum, dout, dbias_out, rows);
+    launch_pdl(k, dim3(blocks < grid_cap ? blocks : grid_cap), dim3(RW_WARPS * 32), smem, s, g, g_is_f32, x, w, mean, rstd, dres,
+               dx, dw, db, o, o_is_f32, gate, dgate_accum, dout, dbias_out, rows);
   } else {
     auto k = ln_bwd_split_kernel<NVW, W, false>;
     static int grid_cap = 0;
     if (!grid_cap) grid_cap = resident_grid(k, smem, 1 << 30, GROUPS);
     const int blocks = (rows + GROUPS - 1) / GROUPS;
-    k<<<blocks < grid_cap ? blocks : grid_cap, RW_WARPS * 32, smem, s>>>(g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db,
-                                                                          nullptr, 0, nullptr, nullptr, nullptr, nullptr, rows);
+    launch_pdl(k, dim3(blocks < grid_cap ? blocks : grid_cap), dim3(RW_WARPS * 32), smem, s, g, g_is_f32, x, w, mean, rstd, dres,
+               dx, dw, db, nullptr, 0, nullptr, nullptr, nullptr, nullptr, rows);
   }
   return check_launch();
 }
@@ -372,6 +376,8 @@ __global__ void __launch_bounds__(RW_WARPS * 32)
 gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_is_f32, const float* __restrict__ gate,
                 float* __restrict__ dgate_accum, void* __restrict__ dout, int out_is_f32, float* __restrict__ dbias,
                 int rows, const DropCfg drop) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int D = 128 * NV;
   extern __shared__ float sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -416,23 +422,27 @@ int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, fl
   const size_t smem = sizeof(float) * RW_WARPS * D;
   int grid = 1;
   GXA_NV_DISPATCH(D, (grid = resident_grid(gate_bwd_kernel<NV>, smem, rows, RW_WARPS)));
-  GXA_NV_DISPATCH(D, (gate_bwd_kernel<NV><<<grid, RW_WARPS * 32, smem, s>>>(dy, f, f_is_f32, gate, dgate_accum, dout,
-                                                                            out_is_f32, dbias, rows, drop)));
+  GXA_NV_DISPATCH(D, (launch_pdl(gate_bwd_kernel<NV>, dim3(grid), dim3(RW_WARPS * 32), smem, s, dy, f, f_is_f32, gate, dgate_accum, dout,
+                                 out_is_f32, dbias, rows, drop)));
   return check_launch();
 }
 
 __global__ void gate_finish_kernel(const float* gate, const float* accum, float* dgate) {
+  pdl_launch_dependents();
+  pdl_wait();
   const float t = tanhf(gate[0]);
   dgate[0] += (1.0f - t * t) * accum[0];
 }
 int gate_finish(const float* gate, const float* accum, float* dgate, cudaStream_t s) {
-  gate_finish_kernel<<<1, 1, 0, s>>>(gate, accum, dgate);
+  launch_pdl(gate_finish_kernel, dim3(1), dim3(1), 0, s, gate, accum, dgate);
   return check_launch();
 }
 
 // ------------------------------------------------------------------ column sums: dst[c] += sum_r src[r, c]
 __global__ void __launch_bounds__(128) colsum_kernel(const void* __restrict__ src, int is_f32, int ld,
                                                      float* __restrict__ dst, int rows, int cols, int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int c = (blockIdx.x * 128 + threadIdx.x) * 2;
   if (c >= cols) return;
   const int r0 = blockIdx.y * rows_per_block;
@@ -462,12 +472,14 @@ int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, 
   if (gy > (rows + 31) / 32) gy = (rows + 31) / 32;
   if (gy < 1) gy = 1;
   const int rpb = (rows + gy - 1) / gy;
-  colsum_kernel<<<dim3(gx, gy), 128, 0, s>>>(src, is_f32, ld, dst, rows, cols, rpb);
+  launch_pdl(colsum_kernel, dim3(gx, gy), dim3(128), 0, s, src, is_f32, ld, dst, rows, cols, rpb);
   return check_launch();
 }
 
 // ------------------------------------------------------------------ casts / elementwise (n % 4 == 0)
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n4) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x)
     st4_bf16(dst + 4 * i, ld4(src + 4 * i));
 }
@@ -487,6 +499,8 @@ struct CastSegs {
   size_t end4[4];          // cumulative float4 counts
 };
 __global__ void cast_segs_kernel(const CastSegs segs) {
+  pdl_launch_dependents();
+  pdl_wait();
   const size_t total = segs.end4[3];
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
     int k = 0;
@@ -513,13 +527,13 @@ int cast_f32_bf16_multi(const float* const* src, void* const* dst, const size_t*
     segs.end4[j] = acc;
   }
   if (acc == 0) return 0;
-  cast_segs_kernel<<<ew_grid(acc), 256, 0, s>>>(segs);
+  launch_pdl(cast_segs_kernel, dim3(ew_grid(acc)), dim3(256), 0, s, segs);
   return check_launch();
 }
 int cast_f32_bf16(const float* src, void* dst, size_t n, cudaStream_t s) {
   if (n % 4) return GXA_ERR_SHAPE;
   if (n == 0) return 0;
-  cast_f32_bf16_kernel<<<ew_grid(n / 4), 256, 0, s>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n / 4);
+  launch_pdl(cast_f32_bf16_kernel, dim3(ew_grid(n / 4)), dim3(256), 0, s, src, reinterpret_cast<__nv_bfloat16*>(dst), n / 4);
   return check_launch();
 }
 int cast_bf16_f32(const void* src, float* dst, size_t n, cudaStream_t s) {
