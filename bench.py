@@ -16,6 +16,8 @@ from __future__ import annotations
 import argparse
 import json
 import os
+
+os.environ.setdefault("NCCL_MAX_CTAS", "16")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
 import statistics
 import subprocess
 import sys

@@ -81,6 +81,11 @@ const char* gxa_version(void);
 const char* gxa_last_cuda_error(void);
 /* number of kernels this library has launched in the calling process (bench.py gpu_launches) */
 long long gxa_launch_count(void);
+/* Persistent kernels size their grids to the SMs they can expect to own.  While another resident kernel holds some
+ * (the NCCL all-reduce of the data-parallel gradient buckets, reference train.py:319 DDPStrategy), the caller lowers
+ * the budget so that no CTA of a statically partitioned grid has to wait for a second wave.  n_sms <= 0 restores the
+ * whole device; returns the previous limit. */
+int gxa_set_sm_limit(int n_sms);
 
 /* ---- sizes ------------------------------------------------------------------------ */
 /* bytes of the per-layer bf16 (or split) weight cache written by gxa_block_prepare_weights */

@@ -39,6 +39,7 @@ SIGNATURES = {
     "gxa_version": (C.c_char_p, []),
     "gxa_last_cuda_error": (C.c_char_p, []),
     "gxa_launch_count": (C.c_longlong, []),
+    "gxa_set_sm_limit": (C.c_int, [C.c_int]),
     "gxa_block_wcache_bytes": (_sz, [_dp]),
     "gxa_block_saved_bytes": (_sz, [_dp]),
     "gxa_block_workspace_bytes": (_sz, [_dp]),
@@ -97,3 +98,8 @@ def check(code: int, what: str) -> None:
 
 def launch_count() -> int:
     return int(lib().gxa_launch_count())
+
+
+def set_sm_limit(n_sms: int) -> int:
+    """SMs the persistent grids may assume (0 = all); returns the previous limit (include/gxa.h)."""
+    return int(lib().gxa_set_sm_limit(int(n_sms)))

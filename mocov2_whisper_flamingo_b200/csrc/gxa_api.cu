@@ -24,6 +24,7 @@ bool pdl_enabled() {
   static const int force = [] { const char* e = getenv("GXA_PDL"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
   return force >= 0 ? force == 1 : g_pdl_small;
 }
+static std::atomic<int> g_sm_limit{0};   // gxa_set_sm_limit: SMs the persistent grids may assume (0 = all)
 int num_sms() {
   if (g_sms == 0) {
     int dev = 0, n = 0;
@@ -33,7 +34,8 @@ int num_sms() {
     else
       g_sms = 148;
   }
-  return g_sms;
+  const int lim = g_sm_limit.load(std::memory_order_relaxed);
+  return lim > 0 && lim < g_sms ? lim : g_sms;
 }
 static int fail(int code) {
   cudaError_t e = cudaPeekAtLastError();
@@ -357,6 +359,7 @@ int gxa_query_caps(int* sm_count, int* cc_major, int* cc_minor) {
 const char* gxa_version(void) { return "gxa-b200 0.1 (sm_100a; tcgen05+TMA GEMMs)"; }
 const char* gxa_last_cuda_error(void) { return g_err; }
 long long gxa_launch_count(void) { return g_launches.load(); }
+int gxa_set_sm_limit(int n_sms) { return g_sm_limit.exchange(n_sms < 0 ? 0 : n_sms); }
 
 size_t gxa_block_wcache_bytes(const gxa_dims* d) {
   if (check_dims(d)) return 0;

@@ -316,15 +316,17 @@ static int ln_bwd_split_launch(const void* g, int g_is_f32, const float* x, cons
   const size_t smem = sizeof(float) * GROUPS * D;
   if (o != nullptr) {
     auto k = ln_bwd_split_kernel<NVW, W, true>;
-    static int grid_cap = 0;
-    if (!grid_cap) grid_cap = resident_grid(k, smem, 1 << 30, GROUPS);
+    static int per_sm = 0;
+    if (!per_sm) per_sm = resident_grid(k, smem, 1 << 30, GROUPS) / num_sms();
+    const int grid_cap = per_sm * num_sms();
     const int blocks = (rows + GROUPS - 1) / GROUPS;
     launch_pdl(k, dim3(blocks < grid_cap ? blocks : grid_cap), dim3(RW_WARPS * 32), smem, s, g, g_is_f32, x, w, mean, rstd, dres,
                dx, dw, db, o, o_is_f32, gate, dgate_accum, dout, dbias_out, rows);
   } else {
     auto k = ln_bwd_split_kernel<NVW, W, false>;
-    static int grid_cap = 0;
-    if (!grid_cap) grid_cap = resident_grid(k, smem, 1 << 30, GROUPS);
+    static int per_sm = 0;
+    if (!per_sm) per_sm = resident_grid(k, smem, 1 << 30, GROUPS) / num_sms();
+    const int grid_cap = per_sm * num_sms();
     const int blocks = (rows + GROUPS - 1) / GROUPS;
     launch_pdl(k, dim3(blocks < grid_cap ? blocks : grid_cap), dim3(RW_WARPS * 32), smem, s, g, g_is_f32, x, w, mean, rstd, dres,
                dx, dw, db, nullptr, 0, nullptr, nullptr, nullptr, nullptr, rows);

@@ -7,11 +7,18 @@ stream (ordered after the layer's kernels by an event), so the NVLink/NVSwitch t
 overlaps the backward kernels of layers i-1 .. 0.  ``finish()`` makes the compute stream wait for the
 communication stream and reduces the few stack-level parameters (audio_proj, video_proj, ln_post).
 
+SM budget: the NCCL kernel keeps its CTAs (NCCL_MAX_CTAS, default taken as 16) resident while a bucket is in flight.
+The library's persistent kernels partition their work statically over the CTAs they launch, so a CTA that has to wait
+for an SM held by NCCL doubles that kernel's time.  From the first bucket until ``finish()`` the library is therefore
+told to size its grids for ``SMs - comm_sms`` (``gxa_set_sm_limit``); forward and the first backward layer use the
+whole device.  Measured at c3, 8 GPUs: see DESIGN.md section 6.
+
 Use ``zero_grad(set_to_none=True)`` (torch's default): autograd then adopts the bucket views as
 ``.grad`` without copying, and the in-place all-reduce lands directly in ``.grad``.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional
 
 import torch
@@ -19,7 +26,8 @@ import torch.distributed as dist
 
 
 class DataParallelGrads:
-    def __init__(self, fusion, process_group: Optional[dist.ProcessGroup] = None, average: bool = True):
+    def __init__(self, fusion, process_group: Optional[dist.ProcessGroup] = None, average: bool = True,
+                 comm_sms: Optional[int] = None):
         self.fusion = fusion
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
@@ -27,11 +35,17 @@ class DataParallelGrads:
         self.comm_stream = torch.cuda.Stream() if torch.cuda.is_available() else None
         self.pending: List = []
         self.buckets: List[torch.Tensor] = []
+        # diagnostics only (tools/, never bench.py's reported line): time the step without the collective
+        if comm_sms is None:
+            comm_sms = int(os.environ.get("GXA_DP_COMM_SMS", os.environ.get("NCCL_MAX_CTAS", "16")))
+        self.comm_sms = max(0, comm_sms)
+        self._limited = False
+        self._diag_skip = os.environ.get("GXA_DP_DIAG_NO_ALLREDUCE") == "1"
         fusion.grad_hook = self._on_layer_grads
 
     # called from BlockFn.backward (autograd thread) right after the layer's kernels were enqueued
     def _on_layer_grads(self, token, bucket: torch.Tensor) -> None:
-        if self.world == 1:
+        if self.world == 1 or self._diag_skip:
             return
         if self.comm_stream is None:           # CPU/gloo (tests): synchronous
             if self.average:
@@ -40,11 +54,16 @@ class DataParallelGrads:
             return
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream())
+        if not self._limited and self.comm_sms > 0:      # kernels enqueued from here on share the device with NCCL
+            from . import _lib
+            sms = torch.cuda.get_device_properties(bucket.device).multi_processor_count
+            _lib.set_sm_limit(max(2, sms - self.comm_sms))
+            self._limited = True
         with torch.cuda.stream(self.comm_stream):
             self.comm_stream.wait_event(ready)
-            if self.average:
-                bucket.div_(self.world)
-            self.pending.append(dist.all_reduce(bucket, group=self.pg, async_op=True))
+            # NCCL averages inside the collective: no separate pass over the bucket on the communication stream
+            op = dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM
+            self.pending.append(dist.all_reduce(bucket, op=op, group=self.pg, async_op=True))
         bucket.record_stream(self.comm_stream)
         self.buckets.append(bucket)
 
@@ -68,6 +87,10 @@ class DataParallelGrads:
             for g in rest:
                 g.copy_(flat[o:o + g.numel()].view_as(g))
                 o += g.numel()
+        if self._limited:
+            from . import _lib
+            _lib.set_sm_limit(0)
+            self._limited = False
         for w in self.pending:
             w.wait()                           # makes the current stream wait for the collective
         if self.comm_stream is not None:
