@@ -286,52 +286,50 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         mbar_wait(&sm.sdp_full, g & 1);
         if (warp == 0) STAMP(1, 1);
         tc_fence_after();
-        uint32_t sr[32], dr[32];
-        tmem_ld_32x32(tm_s + lane_addr + cq * 32, sr);
-        tmem_ld_32x32(tm_dp + lane_addr + cq * 32, dr);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.sdp_free);
-        if (warp == 0) STAMP(1, 6);
-        float pv[32], dsv[32];
+        // two 16-column halves: the packed bf16 results of the first half (16 registers) wait in registers while the second
+        // half is loaded and computed, so the working set stays below the 80-register cap of this 704-thread CTA
+        // (one 32-column pass needed 64 raw + 32 result registers and spilled ~40 local-memory accesses per iteration,
+        // which go through the same L1/shared-memory pipe the MMA operands are fetched from)
         const float nls = -ls * kLog2e;
-        // packed f32x2 arithmetic (FFMA2 / FMUL2 / FADD2): half the issue slots of the scalar forms; the compute warps'
-        // instruction stream is on the critical path of every iteration
         const float2 c2 = make_float2(kScaleLog2, kScaleLog2), nls2 = make_float2(nls, nls), nde2 = make_float2(-de, -de);
+        uint32_t ppk[16], dpk[16];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          float2 sv = make_float2(__uint_as_float(sr[2 * c]), __uint_as_float(sr[2 * c + 1]));
-          if (any_masked) sv = __fadd2_rn(sv, *reinterpret_cast<const float2*>(kbias + 2 * c));
-          const float2 e = __ffma2_rn(sv, c2, nls2);
-          pv[2 * c] = ex2a(e.x);
-          pv[2 * c + 1] = ex2a(e.y);
-        }
-        if (drop.thresh == 0) {
-#pragma unroll
-          for (int c = 0; c < 16; ++c) {
-            const float2 d = __fadd2_rn(make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1])), nde2);
-            const float2 t = __fmul2_rn(make_float2(pv[2 * c], pv[2 * c + 1]), d);
-            dsv[2 * c] = t.x;
-            dsv[2 * c + 1] = t.y;
+        for (int hf = 0; hf < 2; ++hf) {
+          uint32_t sr[16], dr[16];
+          tmem_ld_32x16(tm_s + lane_addr + cq * 32 + hf * 16, sr);
+          tmem_ld_32x16(tm_dp + lane_addr + cq * 32 + hf * 16, dr);
+          tmem_ld_wait();
+          if (hf == 1) {                  // S / dP are in registers: the MMA warp may overwrite them
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.sdp_free);
+            if (warp == 0) STAMP(1, 6);
           }
-        } else {
-          // dropout on the probabilities (forward: ctx = (m*P) V): dV sees m*P, dP = m * (dO V^T); same mask as forward
-          const uint32_t ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) *
-                                   static_cast<uint32_t>((Lk + 1) >> 1) + ((cur.k0 + cq * 32) >> 1);
+          uint32_t ctr = 0;
+          if (drop.thresh != 0)           // dropout counter of (row, key pair): same function as the forward (gxa_rng.cuh)
+            ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) * static_cast<uint32_t>((Lk + 1) >> 1) +
+                  ((cur.k0 + cq * 32 + hf * 16) >> 1);
 #pragma unroll
-          for (int c = 0; c < 16; ++c) {
-            bool k0, k1;
-            drop_keep(drop, ctr + c, k0, k1);
-            // dS = P*(m*dP - delta) = (m*P)*dP - P*delta ;  the P tile for dV holds m*P
-            const float2 p0 = make_float2(pv[2 * c], pv[2 * c + 1]);
-            const float2 t = __fmul2_rn(p0, nde2);
-            const float2 pm = __fmul2_rn(p0, make_float2(k0 ? drop.scale : 0.f, k1 ? drop.scale : 0.f));
-            const float2 d = __ffma2_rn(pm, make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1])), t);
-            pv[2 * c] = pm.x;
-            pv[2 * c + 1] = pm.y;
-            dsv[2 * c] = d.x;
-            dsv[2 * c + 1] = d.y;
+          for (int c = 0; c < 8; ++c) {   // packed f32x2 arithmetic (FFMA2 / FMUL2 / FADD2): half the issue slots
+            float2 sv = make_float2(__uint_as_float(sr[2 * c]), __uint_as_float(sr[2 * c + 1]));
+            if (any_masked) sv = __fadd2_rn(sv, *reinterpret_cast<const float2*>(kbias + hf * 16 + 2 * c));
+            const float2 e = __ffma2_rn(sv, c2, nls2);
+            float2 pe = make_float2(ex2a(e.x), ex2a(e.y));
+            const float2 dp = make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1]));
+            float2 ds;
+            if (drop.thresh == 0) {
+              ds = __fmul2_rn(pe, __fadd2_rn(dp, nde2));
+            } else {
+              // dropout on the probabilities (forward: ctx = (m*P) V): dV sees m*P, dP = m * (dO V^T)
+              // dS = P*(m*dP - delta) = (m*P)*dP - P*delta ;  the P tile for dV holds m*P
+              bool k0, k1;
+              drop_keep(drop, ctr + c, k0, k1);
+              const float2 t = __fmul2_rn(pe, nde2);
+              pe = __fmul2_rn(pe, make_float2(k0 ? drop.scale : 0.f, k1 ? drop.scale : 0.f));
+              ds = __ffma2_rn(pe, dp, t);
+            }
+            ppk[hf * 8 + c] = pk2(pe.x, pe.y);
+            dpk[hf * 8 + c] = pk2(ds.x, ds.y);
           }
         }
         if (warp == 0) STAMP(1, 2);
@@ -340,13 +338,11 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int gg = 0; gg < 4; ++gg) {
           const int chunk = (cq & 1) * 4 + gg;
           const uint32_t sw = (chunk ^ (r & 7)) << 4;
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_row + sw),
-                       "r"(pk2(pv[8 * gg + 0], pv[8 * gg + 1])), "r"(pk2(pv[8 * gg + 2], pv[8 * gg + 3])),
-                       "r"(pk2(pv[8 * gg + 4], pv[8 * gg + 5])), "r"(pk2(pv[8 * gg + 6], pv[8 * gg + 7]))
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_row + sw), "r"(ppk[4 * gg]), "r"(ppk[4 * gg + 1]),
+                       "r"(ppk[4 * gg + 2]), "r"(ppk[4 * gg + 3])
                        : "memory");
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(s_row + sw),
-                       "r"(pk2(dsv[8 * gg + 0], dsv[8 * gg + 1])), "r"(pk2(dsv[8 * gg + 2], dsv[8 * gg + 3])),
-                       "r"(pk2(dsv[8 * gg + 4], dsv[8 * gg + 5])), "r"(pk2(dsv[8 * gg + 6], dsv[8 * gg + 7]))
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(s_row + sw), "r"(dpk[4 * gg]), "r"(dpk[4 * gg + 1]),
+                       "r"(dpk[4 * gg + 2]), "r"(dpk[4 * gg + 3])
                        : "memory");
         }
         fence_proxy_async_smem();
