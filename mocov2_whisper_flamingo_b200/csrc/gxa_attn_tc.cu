@@ -334,6 +334,21 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   pdl_wait();                           // prologue done; everything below reads / writes global memory
   const int kend = kv_end ? min(kv_end[b], Lk) : Lk;
   const int nblk = (kend + TC_BK - 1) / TC_BK;
+  // the first two key blocks need no ring slot to be released: issue Q and those K / V tiles before the key-visibility
+  // pass below, so that their HBM latency overlaps it (the first S is on every CTA's critical path)
+  auto load_kv = [&](int j) {
+    const int st = j & 1;
+    mbar_arrive_expect_tx(&sm.k_full[st], TC_TILE);
+    tma_load_3d(sm.k[st], &tmKV, &sm.k_full[st], h * TC_HD, j * TC_BK, b);
+    mbar_arrive_expect_tx(&sm.v_full[st], TC_TILE);
+    tma_load_3d(sm.v[st], &tmKV, &sm.v_full[st], D + h * TC_HD, j * TC_BK, b);
+  };
+  if (warp == TC_SOFTMAX_WARPS && lane == 0 && nblk > 0) {
+    mbar_arrive_expect_tx(&sm.q_full, TC_TILE);
+    tma_load_3d(sm.q, &tmQ, &sm.q_full, h * TC_HD, q0, b);
+    load_kv(0);
+    if (nblk > 1) load_kv(1);
+  }
   {
     const uint8_t* mg = mask ? mask + size_t(b) * Lk : nullptr;
     for (int key = threadIdx.x; key < nblk * TC_BK; key += TC_FWD_THREADS) {
@@ -350,10 +365,8 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   if (warp == TC_SOFTMAX_WARPS) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0 && nblk > 0) {
-      mbar_arrive_expect_tx(&sm.q_full, TC_TILE);
-      tma_load_3d(sm.q, &tmQ, &sm.q_full, h * TC_HD, q0, b);
-      for (int j = 0; j < nblk; ++j) {
+    if (lane == 0) {
+      for (int j = 2; j < nblk; ++j) {           // blocks 0 and 1 were issued in the prologue
         const int st = j & 1;
         const uint32_t ph = ((j >> 1) & 1) ^ 1;
         mbar_wait(&sm.k_empty[st], ph);
