@@ -42,7 +42,7 @@ struct Smem {
   float kbias[2][BK];              // 0 for a visible key, -inf for a padded / masked one
   int kb_any[2][DRAIN_WARPS];
   uint64_t kv_full[2], kv_empty[2], q_full[QSTAGES], q_empty[QSTAGES];
-  uint64_t sdp_full, sdp_free, pds_ready, pds_free, dq_full[2], dq_free[2], dkv_full, dkv_free, kb_full[2];
+  uint64_t sdp_full, sdp_free, pds_ready, p_free, pds_free, dq_full[2], dq_free[2], dkv_full, dkv_free, kb_full[2];
   uint32_t tmem_slot;
   uint8_t live[MAX_ITEMS];         // this CTA's items: 0 = the whole key block is padding
 };
@@ -103,7 +103,7 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
     for (int i = 0; i < QSTAGES; ++i) { mbar_init(&sm.q_full[i], 1); mbar_init(&sm.q_empty[i], 1); }
     mbar_init(&sm.sdp_full, 1); mbar_init(&sm.sdp_free, COMPUTE_WARPS);
-    mbar_init(&sm.pds_ready, COMPUTE_WARPS); mbar_init(&sm.pds_free, 1);
+    mbar_init(&sm.pds_ready, COMPUTE_WARPS); mbar_init(&sm.pds_free, 1); mbar_init(&sm.p_free, 1);
     mbar_init(&sm.dkv_full, 1); mbar_init(&sm.dkv_free, DRAIN_WARPS);
     mbar_fence_init();
   }
@@ -226,6 +226,7 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
           for (int k = 0; k < 8; ++k)     // contraction over the 128 queries, 16 per step (rows of P / dS / dO / Q)
             umma_bf16_e(tm_dv, p_t + k * 128, HI, om + k * 128, HI, id_t, k > 0 ? 1u : acc0, el);
+          umma_commit_e(&sm.p_free, el);  // P is read by dV only: the compute warps may store the next P while dK / dQ run
 #pragma unroll
           for (int k = 0; k < 8; ++k)
             umma_bf16_e(tm_dk, s_t + k * 128, HI, qm + k * 128, HI, id_t, k > 0 ? 1u : acc0, el);
@@ -333,14 +334,18 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
         }
         if (warp == 0) STAMP(1, 2);
-        if (g > 0) mbar_wait(&sm.pds_free, (g - 1) & 1);     // previous dV/dK/dQ MMAs no longer read P / dS
+        if (g > 0) mbar_wait(&sm.p_free, (g - 1) & 1);       // previous dV MMAs no longer read P
 #pragma unroll
         for (int gg = 0; gg < 4; ++gg) {
-          const int chunk = (cq & 1) * 4 + gg;
-          const uint32_t sw = (chunk ^ (r & 7)) << 4;
+          const uint32_t sw = (((cq & 1) * 4 + gg) ^ (r & 7)) << 4;
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_row + sw), "r"(ppk[4 * gg]), "r"(ppk[4 * gg + 1]),
                        "r"(ppk[4 * gg + 2]), "r"(ppk[4 * gg + 3])
                        : "memory");
+        }
+        if (g > 0) mbar_wait(&sm.pds_free, (g - 1) & 1);     // previous dK / dQ MMAs no longer read dS
+#pragma unroll
+        for (int gg = 0; gg < 4; ++gg) {
+          const uint32_t sw = (((cq & 1) * 4 + gg) ^ (r & 7)) << 4;
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(s_row + sw), "r"(dpk[4 * gg]), "r"(dpk[4 * gg + 1]),
                        "r"(dpk[4 * gg + 2]), "r"(dpk[4 * gg + 3])
                        : "memory");
@@ -411,20 +416,22 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tc_fence_after();
         // staging layout = accumulator layout [16 column groups][128 rows][4 floats]: conflict-free 16-byte stores
         const uint32_t st_row = smem_u32(sm.qdo[qs]) + r * 16;
-#pragma unroll
-        for (int c = 0; c < HD; c += 32) {
-          uint32_t a[32];
-          tmem_ld_32x32(tm_dq + (g & 1) * 64 + lane_addr + c, a);
+        {   // both halves of the 64 accumulator columns in flight at once: one TMEM latency on the ring slot's way back
+          uint32_t a0[32], a1[32];
+          tmem_ld_32x32(tm_dq + (g & 1) * 64 + lane_addr, a0);
+          tmem_ld_32x32(tm_dq + (g & 1) * 64 + lane_addr + 32, a1);
           tmem_ld_wait();
-          if (c == 32) {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&sm.dq_free[g & 1]);
-          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.dq_free[g & 1]);
 #pragma unroll
           for (int j = 0; j < 8; ++j)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(st_row + ((c >> 2) + j) * (BQ * 16)), "r"(a[4 * j]),
-                         "r"(a[4 * j + 1]), "r"(a[4 * j + 2]), "r"(a[4 * j + 3]) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(st_row + j * (BQ * 16)), "r"(a0[4 * j]),
+                         "r"(a0[4 * j + 1]), "r"(a0[4 * j + 2]), "r"(a0[4 * j + 3]) : "memory");
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(st_row + (8 + j) * (BQ * 16)), "r"(a1[4 * j]),
+                         "r"(a1[4 * j + 1]), "r"(a1[4 * j + 2]), "r"(a1[4 * j + 3]) : "memory");
         }
         fence_proxy_async_smem();
         asm volatile("bar.sync 2, 128;" ::: "memory");
@@ -436,7 +443,8 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
         if (++qs == QSTAGES) qs = 0;
       }
-      // ---- dV then dK of this item (thread = key row)
+      // ---- dV then dK of this item (thread = key row).  (Tried: draining them before the item's last dQ tile, and on the
+      // 16 compute warps -- both slower: the Q/dO ring slot that the dQ tile is staged in must go back to the producer first.)
       mbar_wait(&sm.dkv_full, n & 1);
       tc_fence_after();
       const int key = cur.k0 + r;
