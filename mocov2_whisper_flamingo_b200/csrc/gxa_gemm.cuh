@@ -22,8 +22,8 @@ enum Epilogue : int {
   EPI_BF16 = 0,       // C(bf16) = acc + bias
   EPI_F32 = 1,        // C(f32)  = acc + bias          (atomic add when accumulate / split-K)
   EPI_GATE_RES = 2,   // t = bf16(acc + bias) -> C2(bf16);  C(f32) = aux(f32) + tanh(gate) * t
-  EPI_BIAS_GELU = 3,  // u = bf16(acc + bias) -> C(bf16);   C2(bf16) = gelu_erf(u)
-  EPI_GELU_BWD = 4,   // C(bf16) = bf16(acc) * gelu'(aux(bf16))
+  EPI_BIAS_GELU = 3,  // u = bf16(acc + bias);   C2(bf16) = gelu_erf(u);   C(bf16) = gelu_erf'(u), all the backward needs of u
+  EPI_GELU_BWD = 4,   // C(bf16) = bf16(acc) * aux(bf16),  aux = gelu'(u) as stored by EPI_BIAS_GELU
 };
 
 struct GemmParams {
@@ -135,11 +135,14 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
                           x.w + gate_t * v[4 * i + 3]);
     }
   } else if constexpr (EPI == EPI_BIAS_GELU) {
+    float dg[32];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = bf16r(v[i]);
-    store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C) + off, v);
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+    for (int i = 0; i < 32; ++i) {
+      v[i] = bf16r(v[i]);
+      dg[i] = gelu_erf_grad(v[i]);
+      v[i] = gelu_erf(v[i]);
+    }
+    store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C) + off, dg);
     store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + col, v);
   } else if constexpr (EPI == EPI_GELU_BWD) {
     const uint4* u4 = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
@@ -150,9 +153,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
       const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float2 u = __bfloat1622float2(h[j]);
-        v[8 * i + 2 * j] = bf16r(v[8 * i + 2 * j]) * gelu_erf_grad(u.x);
-        v[8 * i + 2 * j + 1] = bf16r(v[8 * i + 2 * j + 1]) * gelu_erf_grad(u.y);
+        float2 dg = __bfloat1622float2(h[j]);
+        v[8 * i + 2 * j] = bf16r(v[8 * i + 2 * j]) * dg.x;
+        v[8 * i + 2 * j + 1] = bf16r(v[8 * i + 2 * j + 1]) * dg.y;
       }
     }
     store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C) + off, v);
@@ -204,6 +207,16 @@ __device__ __forceinline__ float2 gelu_grad_fast2(float2 u) {
   const float2 q = __fadd2_rn(nh, f2(0.5f));                        // 0.5 - h >= 0
   const float2 cdf = __fadd2_rn(make_float2(copysignf(q.x, u.x), copysignf(q.y, u.y)), f2(0.5f));
   return __ffma2_rn(__fmul2_rn(u, f2(0.3989422804014327f)), e, cdf);
+}
+// value and derivative from one exponential / reciprocal / polynomial
+__device__ __forceinline__ void gelu_both2(float2 u, float2& g, float2& dg) {
+  const float2 au = make_float2(fabsf(u.x), fabsf(u.y));
+  float2 e;
+  const float2 nh = gelu_neg_h2(u, au, e);
+  g = __ffma2_rn(au, nh, make_float2(fmaxf(u.x, 0.f), fmaxf(u.y, 0.f)));
+  const float2 q = __fadd2_rn(nh, f2(0.5f));
+  const float2 cdf = __fadd2_rn(make_float2(copysignf(q.x, u.x), copysignf(q.y, u.y)), f2(0.5f));
+  dg = __ffma2_rn(__fmul2_rn(u, f2(0.3989422804014327f)), e, cdf);
 }
 __device__ __forceinline__ float gelu_fast(float u) { return gelu_fast2(make_float2(u, u)).x; }
 __device__ __forceinline__ float gelu_grad_fast(float u) { return gelu_grad_fast2(make_float2(u, u)).x; }
@@ -322,17 +335,17 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
       *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + off) =
           make_float4(fmaf(gate_t, a.x, x.x), fmaf(gate_t, a.y, x.y), fmaf(gate_t, a.z, x.z), fmaf(gate_t, a.w, x.w));
     } else if constexpr (EPI == EPI_BIAS_GELU) {
-      const uint2 pk = pack_bf16x4(a);
-      a = unpack_bf16x4(pk);
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pk;
-      const float2 g0 = gelu_fast2(make_float2(a.x, a.y)), g1 = gelu_fast2(make_float2(a.z, a.w));
+      a = round_bf16x4(a);          // u as autocast's bf16 linear output
+      float2 g0, g1, d0, d1;
+      gelu_both2(make_float2(a.x, a.y), g0, d0);
+      gelu_both2(make_float2(a.z, a.w), g1, d1);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(make_float4(d0.x, d0.y, d1.x, d1.y));
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) =
           pack_bf16x4(make_float4(g0.x, g0.y, g1.x, g1.y));
     } else if constexpr (EPI == EPI_GELU_BWD) {
       a = round_bf16x4(a);
-      const float4 u = unpack_bf16x4(ax.v[it]);
-      const float2 g0 = gelu_grad_fast2(make_float2(u.x, u.y)), g1 = gelu_grad_fast2(make_float2(u.z, u.w));
-      const uint2 pk = pack_bf16x4(make_float4(a.x * g0.x, a.y * g0.y, a.z * g1.x, a.w * g1.y));
+      const float4 dg = unpack_bf16x4(ax.v[it]);      // gelu'(u), stored by the forward epilogue
+      const uint2 pk = pack_bf16x4(make_float4(a.x * dg.x, a.y * dg.y, a.z * dg.z, a.w * dg.w));
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pk;
       const float4 orr = unpack_bf16x4(pk);
       cs.x += orr.x; cs.y += orr.y; cs.z += orr.z; cs.w += orr.w;

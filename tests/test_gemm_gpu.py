@@ -80,18 +80,18 @@ def test_epilogue_gate_residual():
 def test_epilogue_bias_gelu_and_backward():
     A, B = operands(260, 1536, 384, seed=5)
     bias = torch.randn(1536, device="cuda")
-    U, Act = gemm(A, B, epi=_lib.EPI_BIAS_GELU, bias=bias)
-    u_ref = (ref_mm(A, B) + bias).to(torch.bfloat16)
-    assert rel_err(U.float(), u_ref.float()) < 8e-3
-    a_ref = torch.nn.functional.gelu(U.float()).to(torch.bfloat16)
-    assert rel_err(Act.float(), a_ref.float()) < 8e-3
-    # GELU backward epilogue: dU = bf16(dA) * gelu'(U), with dA = dF @ W2 (B operand MN-major as in dgrad)
+    # forward epilogue: u = bf16(A B^T + bias);  C2 = gelu(u);  C = gelu'(u) (what the backward needs of u)
+    G, Act = gemm(A, B, epi=_lib.EPI_BIAS_GELU, bias=bias)
+    u_ref = (ref_mm(A, B) + bias).to(torch.bfloat16).float().requires_grad_(True)
+    a_ref = torch.nn.functional.gelu(u_ref)
+    a_ref.sum().backward()
+    assert rel_err(Act.float(), a_ref.detach().to(torch.bfloat16).float()) < 8e-3
+    assert rel_err(G.float(), u_ref.grad.to(torch.bfloat16).float()) < 8e-3
+    # GELU backward epilogue: dU = bf16(dA) * gelu'(u), with dA = dF @ W2 (B operand MN-major as in dgrad)
     dF, W2t = operands(260, 1536, 384, seed=6)           # dF [260,384], W2^T logical [1536,384]
-    dU, _ = gemm(dF, W2t, False, True, epi=_lib.EPI_GELU_BWD, aux=U)
+    dU, _ = gemm(dF, W2t, False, True, epi=_lib.EPI_GELU_BWD, aux=G)
     dA = ref_mm(dF, W2t).to(torch.bfloat16).float()
-    u = U.float().requires_grad_(True)
-    torch.nn.functional.gelu(u).backward(dA)
-    assert rel_err(dU.float(), u.grad) < 1e-2
+    assert rel_err(dU.float(), dA * u_ref.grad) < 1e-2
 
 
 # ---- CTA-pair (cta_group::2) 256x256 kernel, selected with bn=512 ---------------------------------
@@ -123,17 +123,18 @@ def test_pair_kernel_epilogues():
     Cm, _ = gemm(A, B, epi=_lib.EPI_BF16, bias=bias, bn=512)
     R = (ref_mm(A, B) + bias).to(torch.bfloat16)
     assert rel_err(Cm.float(), R.float()) < 8e-3
-    U, Act = gemm(A, B, epi=_lib.EPI_BIAS_GELU, bias=bias, bn=512)
-    assert rel_err(U.float(), R.float()) < 8e-3
-    a_ref = torch.nn.functional.gelu(U.float()).to(torch.bfloat16)
+    G, Act = gemm(A, B, epi=_lib.EPI_BIAS_GELU, bias=bias, bn=512)      # C = gelu'(u), C2 = gelu(u), u = bf16(R)
+    u = R.float().requires_grad_(True)
+    a = torch.nn.functional.gelu(u)
+    a.sum().backward()
+    a_ref = a.detach().to(torch.bfloat16)
     assert rel_err(Act.float(), a_ref.float()) < 8e-3
     assert (Act.float() - a_ref.float()).abs().max() < 2e-2 * a_ref.float().abs().max()
+    assert rel_err(G.float(), u.grad.to(torch.bfloat16).float()) < 8e-3
     dF, W2t = operands(700, 1536, 384, seed=10)
-    dU, _ = gemm(dF, W2t, False, True, epi=_lib.EPI_GELU_BWD, aux=U, bn=512)
+    dU, _ = gemm(dF, W2t, False, True, epi=_lib.EPI_GELU_BWD, aux=G, bn=512)
     dA = ref_mm(dF, W2t).to(torch.bfloat16).float()
-    u = U.float().requires_grad_(True)
-    torch.nn.functional.gelu(u).backward(dA)
-    assert rel_err(dU.float(), u.grad) < 1e-2
+    assert rel_err(dU.float(), dA * u.grad) < 1e-2
     A2, B2 = operands(700, 512, 1536, seed=11)
     b2 = torch.randn(512, device="cuda")
     X = torch.randn(700, 512, device="cuda")
