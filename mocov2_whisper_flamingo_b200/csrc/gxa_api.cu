@@ -183,6 +183,47 @@ struct WCache {
 };
 
 // ================================================================== forward
+// ------------------------------------------------------------------ side stream
+// Work that is off the layer's dependency chain (the K|V projection in forward, the five weight-gradient GEMMs and the
+// d(xa) GEMM in backward) is enqueued on a second stream, forked from and joined to the caller's stream by events inside
+// the call.  Every GEMM is a persistent grid with a static tile split, so its last wave leaves SMs idle (448 tiles on 74
+// CTA pairs = 6.05 waves for the N = 1024 GEMMs at c3); a kernel from the other stream fills them.  Nothing outlives the
+// call: the join is enqueued before returning, so workspace reuse by the next layer stays ordered.  GXA_SIDE_STREAM=0
+// puts everything back on one stream.
+struct SideStream {
+  cudaStream_t s = nullptr;
+  cudaEvent_t fork[8] = {};
+  cudaEvent_t join = nullptr;
+  bool ok = false;
+};
+static SideStream* side_stream() {
+  static const bool enabled = [] { const char* e = getenv("GXA_SIDE_STREAM"); return !(e && e[0] == '0'); }();
+  if (!enabled) return nullptr;
+  static SideStream per_dev[16];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  SideStream& sd = per_dev[dev];
+  if (!sd.ok) {
+    if (cudaStreamCreateWithFlags(&sd.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    for (auto& e : sd.fork)
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&sd.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    sd.ok = true;
+  }
+  return &sd;
+}
+// the side stream, ordered after everything enqueued on `s` so far (or `s` itself when there is no side stream)
+static cudaStream_t side_fork(SideStream* sd, int slot, cudaStream_t s) {
+  if (!sd) return s;
+  if (cudaEventRecord(sd->fork[slot], s) != cudaSuccess || cudaStreamWaitEvent(sd->s, sd->fork[slot], 0) != cudaSuccess) return s;
+  return sd->s;
+}
+static int side_join(SideStream* sd, cudaStream_t s) {
+  if (!sd) return 0;
+  if (cudaEventRecord(sd->join, sd->s) != cudaSuccess || cudaStreamWaitEvent(s, sd->join, 0) != cudaSuccess) return GXA_ERR_CUDA;
+  return 0;
+}
+
 static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const void* wcache, const float* x,
                           const void* xa_op, const uint8_t* mask, const int32_t* kv_end, float* y, void* saved,
                           cudaStream_t s, const bf16* kv_cached = nullptr) {
@@ -195,12 +236,14 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   if (kv_cached != nullptr) S.kv = const_cast<bf16*>(kv_cached);   // ... K|V were projected once (gxa_block_kv_prefill)
   const float* x1 = x;
   if (d.has_xa) {
+    SideStream* sd = kv_cached == nullptr ? side_stream() : nullptr;
+    if (kv_cached == nullptr)       // K|V depend on xa only: side stream, joined before the attention kernel
+      GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, S.kv, 2 * D,
+                        nullptr, 0, p.in_proj_b + D, nullptr, 0, nullptr, 0, side_fork(sd, 0, s)));
     GXA_TRY(ln_fwd(x, p.attn_ln_w, p.attn_ln_b, S.h, 0, S.mean1, S.rstd1, M, D, s));
     GXA_TRY(gemm_bf16(S.h, D, false, W.in_proj, D, false, M, D, D, EPI_BF16, S.q, D, nullptr, 0, p.in_proj_b, nullptr, 0,
                       nullptr, 0, s));
-    if (kv_cached == nullptr)
-      GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, S.kv, 2 * D,
-                        nullptr, 0, p.in_proj_b + D, nullptr, 0, nullptr, 0, s));
+    GXA_TRY(side_join(sd, s));
     GXA_TRY(attn_fwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, D, S.lse, d.B, d.H, d.Lq, d.Lk, s,
                           make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
     GXA_TRY(gemm_bf16(S.ctx, D, false, W.out, D, false, M, D, D, EPI_GATE_RES, S.x1, D, S.o, D, p.out_proj_b, x, D,
@@ -251,6 +294,7 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   WorkBf16 Wk(d, workspace);
   WCache W(d, wcache);
   if (cudaMemsetAsync(Wk.gacc, 0, 64 * sizeof(float), s) != cudaSuccess) return fail(GXA_ERR_CUDA);
+  SideStream* sd = side_stream();    // weight gradients leave the dgrad chain (joined before returning)
   const float* x1 = d.has_xa ? S.x1 : x;
   // ---- FFN branch
   GXA_TRY(gate_bwd(dy, S.f, 0, p.ff_gate, Wk.gacc + 1, Wk.df, 0, g.ff2_b, M, D, s,
@@ -258,16 +302,16 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   GXA_TRY(gemm_bf16(Wk.df, D, false, W.ff2, 4 * D, true, M, 4 * D, D, EPI_GELU_BWD, Wk.du, 4 * D, nullptr, 0, nullptr,
                     S.u, 4 * D, nullptr, 0, s, g.ff0_b));     // d(ff.0.bias) = colsum(du) fused in the epilogue
   GXA_TRY(gemm_bf16(Wk.df, D, true, S.a, 4 * D, true, D, 4 * D, M, EPI_F32, g.ff2_w, 4 * D, nullptr, 0, nullptr, nullptr,
-                    0, nullptr, 1, s));
+                    0, nullptr, 1, side_fork(sd, 0, s)));
   GXA_TRY(gemm_bf16(Wk.du, 4 * D, false, W.ff0, D, true, M, D, 4 * D, EPI_BF16, Wk.dh2, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 0, s));
   GXA_TRY(gemm_bf16(Wk.du, 4 * D, true, S.h2, D, true, 4 * D, D, M, EPI_F32, g.ff0_w, D, nullptr, 0, nullptr, nullptr, 0,
-                    nullptr, 1, s));
+                    nullptr, 1, side_fork(sd, 1, s)));
   GXA_TRY(gate_finish(p.ff_gate, Wk.gacc + 1, g.ff_gate, s));
   if (!d.has_xa) {
     GXA_TRY(ln_bwd(Wk.dh2, 0, x1, p.ff_ln_w, S.mean2, S.rstd2, dy, dx, g.ff_ln_w, g.ff_ln_b, nullptr, 0, nullptr, nullptr,
                    nullptr, nullptr, M, D, s));
-    return 0;
+    return side_join(sd, s);
   }
   // ---- LN2 backward fused with the attention-gate backward: dx1, do = tanh(a)*dx1, d(attn_gate), d(bo)
   GXA_TRY(ln_bwd(Wk.dh2, 0, x1, p.ff_ln_w, S.mean2, S.rstd2, dy, Wk.dx1, g.ff_ln_w, g.ff_ln_b, S.o, 0, p.attn_gate,
@@ -276,24 +320,27 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   GXA_TRY(gemm_bf16(Wk.dob, D, false, W.out, D, true, M, D, D, EPI_BF16, Wk.dctx, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 0, s));
   GXA_TRY(gemm_bf16(Wk.dob, D, true, S.ctx, D, true, D, D, M, EPI_F32, g.out_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
-                    nullptr, 1, s));
+                    nullptr, 1, side_fork(sd, 2, s)));
   // ---- attention core
   GXA_TRY(attn_bwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, Wk.dctx, D, S.lse, Wk.delta, Wk.dq, D,
                         Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s, g.in_proj_b,      // + fused d(bq)
                         make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
-  GXA_TRY(colsum(Wk.dkv, 0, 2 * D, g.in_proj_b + D, Mk, 2 * D, s));
-  GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
-                    nullptr, 1, s));
-  GXA_TRY(gemm_bf16(Wk.dkv, 2 * D, true, xa_op, D, true, 2 * D, D, Mk, EPI_F32, g.in_proj_w + size_t(D) * D, D, nullptr,
-                    0, nullptr, nullptr, 0, nullptr, 1, s));
+  {   // everything that only consumes dq / dkv and is not on the way to dx: side stream
+    const cudaStream_t ws = side_fork(sd, 3, s);
+    GXA_TRY(colsum(Wk.dkv, 0, 2 * D, g.in_proj_b + D, Mk, 2 * D, ws));
+    GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
+                      nullptr, 1, ws));
+    GXA_TRY(gemm_bf16(Wk.dkv, 2 * D, true, xa_op, D, true, 2 * D, D, Mk, EPI_F32, g.in_proj_w + size_t(D) * D, D, nullptr,
+                      0, nullptr, nullptr, 0, nullptr, 1, ws));
+    if (dxa)
+      GXA_TRY(gemm_bf16(Wk.dkv, 2 * D, false, W.in_proj + size_t(D) * D, D, true, Mk, D, 2 * D, EPI_F32, dxa, D, nullptr, 0,
+                        nullptr, nullptr, 0, nullptr, 1, ws));
+  }
   GXA_TRY(gemm_bf16(Wk.dq, D, false, W.in_proj, D, true, M, D, D, EPI_BF16, Wk.dh, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 0, s));
-  if (dxa)
-    GXA_TRY(gemm_bf16(Wk.dkv, 2 * D, false, W.in_proj + size_t(D) * D, D, true, Mk, D, 2 * D, EPI_F32, dxa, D, nullptr, 0,
-                      nullptr, nullptr, 0, nullptr, 1, s));
   GXA_TRY(ln_bwd(Wk.dh, 0, x, p.attn_ln_w, S.mean1, S.rstd1, Wk.dx1, dx, g.attn_ln_w, g.attn_ln_b, nullptr, 0, nullptr,
                  nullptr, nullptr, nullptr, M, D, s));
-  return 0;
+  return side_join(sd, s);
 }
 
 static int block_bwd_f32(const gxa_dims& d, const gxa_block_params& p, const float* x, const void* xa_op,
