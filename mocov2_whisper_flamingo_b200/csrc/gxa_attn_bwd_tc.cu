@@ -7,11 +7,15 @@
 //
 // Per item:  for each 128-query block i
 //   S = Q_i K^T, dP = dO_i V^T            (TMEM cols 0..127, 128..255; refilled as soon as the compute warps read them)
-//   P = exp2(S*c - lse), dS = P*(dP - delta)   16 warps, thread = (query row, 32 key columns)
+//   P = exp2(S*c - lse), dS = P*(dP - delta)   16 warps, thread = (query row, 32 key columns) in two 16-column halves
+//                                           (packed f32x2 math, packed bf16 results held in registers: no spills --
+//                                           local memory shares the L1/smem pipe with the MMA operand fetches, which
+//                                           bound this kernel: tools/mma_rate.cu)
 //   dV += P^T dO_i, dK += dS^T Q_i         (TMEM cols 256..319, 320..383; accumulate over the query blocks; operands
 //                                           are read MN-major through descriptors -> the transposes are free)
-//   dQ_i = dS K                            (TMEM cols 384..447 / 448..511, double-buffered) -> 4 drain warps ->
-//                                           fp32 vector reductions into the [B,H,LqPad,64] accumulator
+//   dQ_i = dS K                            (TMEM cols 384..447 / 448..511, double-buffered) -> 4 drain warps -> staged
+//                                           in the freed Q/dO ring slot -> TMA bulk reduce-add into the fp32
+//                                           [B,H,Lq/128,16,128,4] accumulator (attn_dq_finalize2_kernel converts)
 // warps 0-15 compute, 16-19 drain (dQ every iteration, dK/dV + next key mask at item end), 20 TMA producer
 // (K/V double-buffered per item, Q/dO 3-stage ring), 21 MMA issuer.
 #include <cstdlib>
