@@ -7,7 +7,8 @@ Everything below them is hand-written CUDA behind the C ABI in include/gxa.h.
 from .gate_cross_attention import (GatedCrossAttentionBlock, GatedCrossModalFusion, LayerNorm,  # noqa: F401
                                    set_default_precision)
 from .decode import DecodeState  # noqa: F401
+from .av_glue import fuse_sum, positional_table, proj_ln_pe  # noqa: F401
 from ._lib import LIB_PATH, launch_count  # noqa: F401
 
 __all__ = ["LayerNorm", "GatedCrossAttentionBlock", "GatedCrossModalFusion", "set_default_precision",
-           "DecodeState", "launch_count", "LIB_PATH"]
+           "DecodeState", "proj_ln_pe", "fuse_sum", "positional_table", "launch_count", "LIB_PATH"]

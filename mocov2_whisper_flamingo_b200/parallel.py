@@ -105,3 +105,23 @@ def shard_batch(global_batch: int, rank: int, world: int):
     rem = global_batch % world
     start = rank * per + min(rank, rem)
     return start, start + per + (1 if rank < rem else 0)
+
+
+def balanced_shards(lengths, world: int):
+    """Sample indices per rank for variable-length visual memories (BASELINE config 4).
+
+    The K|V projection and the attention core scale with the sum of the samples' frame counts, so contiguous shards of a
+    length-skewed batch leave ranks unevenly loaded (up to ~30 % at 60..750 frames) and the slowest rank sets the step.
+    Samples are sorted by length, longest first, and dealt to the ranks in a serpentine (0..N-1, N-1..0, ...): every rank
+    gets the same number of samples (+-1) and nearly the same total length.  The reference buckets by frame count for the
+    same reason (``ByFrameCountSampler``, datamodule/data_module.py:18-62).  Pure host logic, no collective: every rank
+    computes the same assignment from the same ``lengths``.
+    """
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    order = sorted(range(len(lengths)), key=lambda i: (-int(lengths[i]), i))
+    shards = [[] for _ in range(world)]
+    for pos, idx in enumerate(order):
+        lap, k = divmod(pos, world)
+        shards[k if lap % 2 == 0 else world - 1 - k].append(idx)
+    return shards

@@ -100,3 +100,23 @@ def test_dropout_mask_restatement_statistics():
     m3 = DR.multipliers(512, 751, 0.1, 0x1234ABCD5678EF01, DR.STREAM_FFN)
     assert abs(np.corrcoef(keep.ravel(), (m3 > 0).ravel())[0, 1]) < 5e-3                 # another stream
     assert np.all(DR.multipliers(4, 9, 0.0, 1, 1) == 1)
+
+
+def test_balanced_shards_even_out_frame_counts():
+    """length-sorted serpentine assignment vs contiguous shards at config-4 lengths (60..750 frames)."""
+    import random
+    from mocov2_whisper_flamingo_b200.parallel import balanced_shards, shard_batch
+    rng = random.Random(1234)
+    lengths = sorted(rng.randint(60, 750) for _ in range(64))          # worst case for contiguous shards: sorted input
+    for world in (1, 2, 4, 8):
+        shards = balanced_shards(lengths, world)
+        assert sorted(i for s in shards for i in s) == list(range(64))                 # a partition
+        assert max(len(s) for s in shards) - min(len(s) for s in shards) <= 1
+        tot = [sum(lengths[i] for i in s) for s in shards]
+        contiguous = [sum(lengths[slice(*shard_batch(64, r, world))]) for r in range(world)]
+        assert max(tot) - min(tot) <= 750                                              # within one sample's length
+        assert max(tot) <= max(contiguous)
+        if world > 1:
+            assert max(tot) / (sum(tot) / world) < 1.05 < 1.3 < max(contiguous) / (sum(contiguous) / world)
+    assert balanced_shards([5, 5, 5], 2) == [[0], [1, 2]]                              # serpentine; ties keep index order
+    assert balanced_shards([], 3) == [[], [], []]

@@ -12,7 +12,7 @@ from oracle import gxa_oracle as O
 from oracle import torch_port as TP
 
 CASES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLDEN, "*.npz"))
-               if not os.path.basename(f).startswith("avnet_"))      # the AVNet fixture has its own layout (below)
+               if not os.path.basename(f).startswith(("avnet_", "avglue")))   # AVNet-level fixtures have their own layout
 
 
 def load(name):
