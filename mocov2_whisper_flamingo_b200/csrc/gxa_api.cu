@@ -162,8 +162,9 @@ static int gemm_f32(const float* A, int lda, bool a_mn, const float* B, int ldb,
 static int gemm_bf16(const void* A, int lda, bool a_mn, const void* B, int ldb, bool b_mn, int M, int N, int K, int epi,
                      void* C, int ldc, void* C2, int ldc2, const float* bias, const void* aux, int ld_aux,
                      const float* gate, int accumulate, cudaStream_t s, float* colsum_out = nullptr,
-                     DropCfg drop = DropCfg{0, 1.f, 0, 0}) {
+                     DropCfg drop = DropCfg{0, 1.f, 0, 0}, int k_splits = 0) {
   GemmOp op;
+  op.k_splits = k_splits;
   op.colsum = colsum_out;
   op.drop = drop;
   op.A = A; op.lda = lda; op.a_mn = a_mn; op.B = B; op.ldb = ldb; op.b_mn = b_mn;
@@ -224,6 +225,23 @@ static int side_join(SideStream* sd, cudaStream_t s) {
   return 0;
 }
 
+// y = x1 + tanh(gate) * (A W^T + bias) for a handful of rows (decode: M = batch x beams).  A 128-row-tile GEMM has only
+// N/128 x ceil(M/128) CTAs there and each walks the whole K (33 us for ff.2 at Whisper-small), so the K range is split
+// over the SMs instead: y <- x1, then every split adds its gated partial with fp32 atomics.  o / f are not rounded to
+// bf16 on this route (nothing is saved for a backward), i.e. it is slightly MORE precise than the training forward.
+static int gated_residual_small_m(const bf16* A, int K, const bf16* Wt, int M, int N, const float* bias, const float* x1,
+                                  const float* gate, float* y, cudaStream_t s) {
+  if (cudaMemcpyAsync(y, x1, sizeof(float) * size_t(M) * N, cudaMemcpyDeviceToDevice, s) != cudaSuccess)
+    return fail(GXA_ERR_CUDA);
+  const int kb = (K + 63) / 64, tiles = ((M + 127) / 128) * ((N + 127) / 128);
+  int ks = num_sms() / (tiles > 0 ? tiles : 1);
+  if (ks > kb / 4) ks = kb / 4;          // at least four 64-wide k-steps per split
+  if (ks > 16) ks = 16;
+  if (ks < 1) ks = 1;
+  return gemm_bf16(A, K, false, Wt, K, false, M, N, K, EPI_F32, y, N, nullptr, 0, bias, nullptr, 0, gate, 1, s, nullptr,
+                   DropCfg{0, 1.f, 0, 0}, ks);
+}
+
 static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const void* wcache, const float* x,
                           const void* xa_op, const uint8_t* mask, const int32_t* kv_end, float* y, void* saved,
                           cudaStream_t s, const bf16* kv_cached = nullptr) {
@@ -234,6 +252,7 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   SavedBf16 S(dc, saved);
   WCache W(d, wcache);
   if (kv_cached != nullptr) S.kv = const_cast<bf16*>(kv_cached);   // ... K|V were projected once (gxa_block_kv_prefill)
+  const bool small_m = kv_cached != nullptr && M <= 256 && d.p_drop == 0.f;   // decode step: split-K gated residuals
   const float* x1 = x;
   if (d.has_xa) {
     SideStream* sd = kv_cached == nullptr ? side_stream() : nullptr;
@@ -246,13 +265,18 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
     GXA_TRY(side_join(sd, s));
     GXA_TRY(attn_fwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, D, S.lse, d.B, d.H, d.Lq, d.Lk, s,
                           make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
-    GXA_TRY(gemm_bf16(S.ctx, D, false, W.out, D, false, M, D, D, EPI_GATE_RES, S.x1, D, S.o, D, p.out_proj_b, x, D,
-                      p.attn_gate, 0, s));
+    if (small_m)
+      GXA_TRY(gated_residual_small_m(S.ctx, D, W.out, M, D, p.out_proj_b, x, p.attn_gate, S.x1, s));
+    else
+      GXA_TRY(gemm_bf16(S.ctx, D, false, W.out, D, false, M, D, D, EPI_GATE_RES, S.x1, D, S.o, D, p.out_proj_b, x, D,
+                        p.attn_gate, 0, s));
     x1 = S.x1;
   }
   GXA_TRY(ln_fwd(x1, p.ff_ln_w, p.ff_ln_b, S.h2, 0, S.mean2, S.rstd2, M, D, s));
   GXA_TRY(gemm_bf16(S.h2, D, false, W.ff0, D, false, M, 4 * D, D, EPI_BIAS_GELU, S.u, 4 * D, S.a, 4 * D, p.ff0_b, nullptr,
                     0, nullptr, 0, s));
+  if (small_m)
+    return gated_residual_small_m(S.a, 4 * D, W.ff2, M, D, p.ff2_b, x1, p.ff_gate, y, s);
   GXA_TRY(gemm_bf16(S.a, 4 * D, false, W.ff2, 4 * D, false, M, D, 4 * D, EPI_GATE_RES, y, D, S.f, D, p.ff2_b, x1, D,
                     p.ff_gate, 0, s, nullptr, make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn)));   // S.f = dropout(f)
   return 0;

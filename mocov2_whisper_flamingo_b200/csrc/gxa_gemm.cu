@@ -128,6 +128,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int half = warp >> 2;            // which half of the BN columns
     float gate_t = 0.f;
     if constexpr (EPI == EPI_GATE_RES) gate_t = tanhf(__ldg(p.gate));
+    if constexpr (EPI == EPI_F32) gate_t = p.gate != nullptr ? tanhf(__ldg(p.gate)) : 1.f;
     int as = 0;
     uint32_t aphase = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x) {
@@ -302,6 +303,7 @@ int gemm_launch(const GemmOp& op, cudaStream_t stream) {
       bn = (op.N % 256 == 0 && num_m * (op.N / 256) >= num_sms()) ? 256 : 128;
     }
   }
+  if (op.epi == EPI_F32 && op.gate != nullptr && bn == 512) bn = 128;   // gated accumulation lives in the 1-CTA epilogue only
   const bool pair = bn == 512;
   int ks = op.k_splits;
   if (ks == 0) {

@@ -20,7 +20,8 @@ namespace gxa {
 
 enum Epilogue : int {
   EPI_BF16 = 0,       // C(bf16) = acc + bias
-  EPI_F32 = 1,        // C(f32)  = acc + bias          (atomic add when accumulate / split-K)
+  EPI_F32 = 1,        // C(f32)  = acc + bias          (atomic add when accumulate / split-K); with `gate` (1-CTA kernel only):
+                      // C += tanh(gate) * (acc + bias) -- the split-K form of EPI_GATE_RES for few-row (decode) problems
   EPI_GATE_RES = 2,   // t = bf16(acc + bias) -> C2(bf16);  C(f32) = aux(f32) + tanh(gate) * t
   EPI_BIAS_GELU = 3,  // u = bf16(acc + bias);   C2(bf16) = gelu_erf(u);   C(bf16) = gelu_erf'(u), all the backward needs of u
   EPI_GELU_BWD = 4,   // C(bf16) = bf16(acc) * aux(bf16),  aux = gelu'(u) as stored by EPI_BIAS_GELU
@@ -102,6 +103,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
     store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C) + off, v);
   } else if constexpr (EPI == EPI_F32) {
     float* c = reinterpret_cast<float*>(p.C) + off;
+    if (p.gate != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] *= gate_t;
+    }
     if (p.accumulate || p.k_splits > 1) {
 #pragma unroll
       for (int i = 0; i < 8; ++i)
