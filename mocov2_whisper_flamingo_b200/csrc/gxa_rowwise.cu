@@ -466,9 +466,93 @@ __global__ void __launch_bounds__(128) colsum_kernel(const void* __restrict__ sr
   atomicAdd(dst + c, a0);
   atomicAdd(dst + c + 1, a1);
 }
+// Wide variant: a thread owns 16 bytes of a row (8 bf16 or 4 fp32 columns) with CS_UNROLL rows per iteration; the block's
+// CS_RY row lanes are folded through shared memory before the atomics.  196 MB of d(k|v) at config 3: the 4-byte-per-thread
+// loop above is latency-bound (~1.4 TB/s, 140 us).  ptxas keeps this one at 32 registers (3-4 loads in flight per thread),
+// so the grid is sized for full residency (8 blocks of 256 threads per SM): ~14 MB of loads outstanding.
+constexpr int CS_TX = 128, CS_RY = 2, CS_UNROLL = 4;
+__device__ __forceinline__ uint4 ldg128_issue(const void* p) {      // streaming 16-byte load, not kept in L1
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+template <bool F32>
+__global__ void __launch_bounds__(CS_TX * CS_RY) colsum_wide_kernel(const void* __restrict__ src, int ld, float* __restrict__ dst,
+                                                                    int rows, int cols, int rows_per_block) {
+  pdl_launch_dependents();
+  pdl_wait();
+  constexpr int VEC = F32 ? 4 : 8;
+  __shared__ float sm[CS_TX * 8];
+  const int tx = threadIdx.x % CS_TX, ry = threadIdx.x / CS_TX;
+  const int c = (blockIdx.x * CS_TX + tx) * VEC;
+  const bool live = c < cols;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  if (live) {
+    const char* base = reinterpret_cast<const char*>(src) + size_t(c) * (F32 ? 4 : 2);
+    const size_t pitch = size_t(ld) * (F32 ? 4 : 2);
+    int r = r0 + ry;
+    const char* q = base + size_t(r) * pitch;
+    const size_t step = pitch * CS_RY;
+    for (; r + (CS_UNROLL - 1) * CS_RY < r1; r += CS_UNROLL * CS_RY) {
+      uint4 v[CS_UNROLL];
+#pragma unroll
+      for (int u = 0; u < CS_UNROLL; ++u) { v[u] = ldg128_issue(q); q += step; }
+#pragma unroll
+      for (int u = 0; u < CS_UNROLL; ++u) {
+        if (F32) {
+          acc[0] += __uint_as_float(v[u].x); acc[1] += __uint_as_float(v[u].y);
+          acc[2] += __uint_as_float(v[u].z); acc[3] += __uint_as_float(v[u].w);
+        } else {
+          acc[0] += __uint_as_float(v[u].x << 16); acc[1] += __uint_as_float(v[u].x & 0xffff0000u);
+          acc[2] += __uint_as_float(v[u].y << 16); acc[3] += __uint_as_float(v[u].y & 0xffff0000u);
+          acc[4] += __uint_as_float(v[u].z << 16); acc[5] += __uint_as_float(v[u].z & 0xffff0000u);
+          acc[6] += __uint_as_float(v[u].w << 16); acc[7] += __uint_as_float(v[u].w & 0xffff0000u);
+        }
+      }
+    }
+    for (; r < r1; r += CS_RY, q += step) {
+      const uint4 v = ldg128_issue(q);
+      if (F32) {
+        acc[0] += __uint_as_float(v.x); acc[1] += __uint_as_float(v.y);
+        acc[2] += __uint_as_float(v.z); acc[3] += __uint_as_float(v.w);
+      } else {
+        acc[0] += __uint_as_float(v.x << 16); acc[1] += __uint_as_float(v.x & 0xffff0000u);
+        acc[2] += __uint_as_float(v.y << 16); acc[3] += __uint_as_float(v.y & 0xffff0000u);
+        acc[4] += __uint_as_float(v.z << 16); acc[5] += __uint_as_float(v.z & 0xffff0000u);
+        acc[6] += __uint_as_float(v.w << 16); acc[7] += __uint_as_float(v.w & 0xffff0000u);
+      }
+    }
+  }
+  if (ry == 1) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) sm[i * CS_TX + tx] = acc[i];
+  }
+  __syncthreads();
+  if (ry == 0 && live) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) atomicAdd(dst + c + i, acc[i] + sm[i * CS_TX + tx]);
+  }
+}
 int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, cudaStream_t s) {
   if (cols % 2) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
+  const int vec = is_f32 ? 4 : 8;
+  static const bool narrow_only = getenv("GXA_COLSUM_NARROW") != nullptr;       // A/B switch (tools/)
+  if (!narrow_only && cols % vec == 0 && ld % vec == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && rows >= 64) {
+    const int gx = (cols / vec + CS_TX - 1) / CS_TX;
+    int gy = (num_sms() * 8 + gx - 1) / gx;
+    const int gy_max = (rows + CS_RY * CS_UNROLL - 1) / (CS_RY * CS_UNROLL);
+    if (gy > gy_max) gy = gy_max;
+    if (gy < 1) gy = 1;
+    const int rpb = (rows + gy - 1) / gy;
+    if (is_f32) launch_pdl(colsum_wide_kernel<true>, dim3(gx, gy), dim3(CS_TX * CS_RY), 0, s, src, ld, dst, rows, cols, rpb);
+    else launch_pdl(colsum_wide_kernel<false>, dim3(gx, gy), dim3(CS_TX * CS_RY), 0, s, src, ld, dst, rows, cols, rpb);
+    return check_launch();
+  }
   const int gx = (cols / 2 + 127) / 128;
   int gy = (num_sms() * 8 + gx - 1) / gx;
   if (gy > (rows + 31) / 32) gy = (rows + 31) / 32;
