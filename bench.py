@@ -310,7 +310,17 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
     ms, clocks = timed(False, args.steps, ClockSampler(local) if rank == 0 else None)
     launches = G.launch_count() - l0
     step(True)
-    ms_e2e, _ = timed(True, args.steps)
+    ms_e2e, clocks_e2e = timed(True, args.steps, ClockSampler(local) if rank == 0 else None)
+    # diagnostic, outside every timed region: what the box's host->device link gives for this step's pinned inputs alone
+    # (e2e hides the copy behind the previous step only if 314 MB move in less than a step)
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    h0.record()
+    bufs[1][0].detach().copy_(audio_h, non_blocking=True)
+    bufs[1][1].detach().copy_(video_h, non_blocking=True)
+    h1.record()
+    torch.cuda.synchronize()
+    h2d_gbs = (audio_h.numel() + video_h.numel()) * 4 / (h0.elapsed_time(h1) * 1e-3) / 1e9
     pk = peaks()
     tokens = GB * Lq
     flops_gpu = 3 * layers * block_fwd_flops(B, Lq, Lk, D)
@@ -329,7 +339,7 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": tokens / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": (audio_h.numel() + video_h.numel()) * 4 + mask_h.numel(),
-                    "d2h_bytes_per_step": 4},
+                    "d2h_bytes_per_step": 4, "h2d_link_gbs_measured": h2d_gbs, "clocks": clocks_e2e},
             "roofline": roof,
             "step_roofline": {"bound": "tensor", "achieved": step_tf, "peak": pk["sustained"], "unit": "TFLOP/s",
                               "frac": step_tf / pk["sustained"], "frac_of_2250_spec": step_tf / 2250.0,

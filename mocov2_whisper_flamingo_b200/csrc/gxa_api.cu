@@ -351,7 +351,9 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
                         make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
   {   // everything that only consumes dq / dkv and is not on the way to dx: side stream
     const cudaStream_t ws = side_fork(sd, 3, s);
-    GXA_TRY(colsum(Wk.dkv, 0, 2 * D, g.in_proj_b + D, Mk, 2 * D, ws));
+    // d(bv) only: d(bk) is identically zero (every row of dS sums to zero -- softmax is invariant to a per-query shift
+    // of the logits; the reference's autograd returns rounding noise there), so the K half is not read
+    GXA_TRY(colsum(Wk.dkv + D, 0, 2 * D, g.in_proj_b + 2 * D, Mk, D, ws));
     GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
                       nullptr, 1, ws));
     GXA_TRY(gemm_bf16(Wk.dkv, 2 * D, true, xa_op, D, true, 2 * D, D, Mk, EPI_F32, g.in_proj_w + size_t(D) * D, D, nullptr,
@@ -397,7 +399,7 @@ static int block_bwd_f32(const gxa_dims& d, const gxa_block_params& p, const flo
   GXA_TRY(attn_bwd_f32(S.q, D, S.kv, S.kv + D, 2 * D, Wk.dctx, D, S.P, Wk.dS, Wk.dq, D, Wk.dkv, Wk.dkv + D, 2 * D, d.B,
                        d.H, d.Lq, d.Lk, s));
   GXA_TRY(colsum(Wk.dq, 1, D, g.in_proj_b, M, D, s));
-  GXA_TRY(colsum(Wk.dkv, 1, 2 * D, g.in_proj_b + D, Mk, 2 * D, s));
+  GXA_TRY(colsum(Wk.dkv + D, 1, 2 * D, g.in_proj_b + 2 * D, Mk, D, s));      // d(bv); d(bk) == 0 (see the bf16 path)
   GXA_TRY(gemm_f32(Wk.dq, D, true, S.h, D, true, D, D, M, g.in_proj_w, D, nullptr, 1, Wk.A3, Wk.B3, s));
   GXA_TRY(gemm_f32(Wk.dkv, 2 * D, true, xa, D, true, 2 * D, D, Mk, g.in_proj_w + size_t(D) * D, D, nullptr, 1, Wk.A3,
                    Wk.B3, s));

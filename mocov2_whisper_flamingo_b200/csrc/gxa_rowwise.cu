@@ -466,15 +466,18 @@ __global__ void __launch_bounds__(128) colsum_kernel(const void* __restrict__ sr
   atomicAdd(dst + c, a0);
   atomicAdd(dst + c + 1, a1);
 }
-// Wide variant: a thread owns 16 bytes of a row (8 bf16 or 4 fp32 columns) with CS_UNROLL rows per iteration; the block's
-// CS_RY row lanes are folded through shared memory before the atomics.  196 MB of d(k|v) at config 3: the 4-byte-per-thread
-// loop above is latency-bound (~1.4 TB/s, 140 us).  ptxas keeps this one at 32 registers (3-4 loads in flight per thread),
-// so the grid is sized for full residency (8 blocks of 256 threads per SM): ~14 MB of loads outstanding.
-constexpr int CS_TX = 128, CS_RY = 2, CS_UNROLL = 4;
-__device__ __forceinline__ uint4 ldg128_issue(const void* p) {      // streaming 16-byte load, not kept in L1
-  uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-  return v;
+// Wide variant: a thread owns 16 bytes of a row (8 bf16 or 4 fp32 columns) and walks every CS_RY-th row of the block's
+// row range.  The loads are cp.async copies into a per-thread ring of CS_STAGES shared-memory slots, so the number of
+// loads in flight is set here and not by the register allocator (a register-array version stayed at 32 registers with
+// 3-4 loads outstanding: 2.4 TB/s for bf16 under ncu, profiles/r01_f_ncu_rowwise.txt; the 4-byte-per-thread loop above:
+// 1.4 TB/s).  A thread only ever reads the slots it filled itself, so cp.async.wait_group is the only synchronisation;
+// the block's CS_RY row lanes are folded through the same shared memory before the atomics.
+constexpr int CS_TX = 128, CS_RY = 2, CS_STAGES = 6;
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_16(uint32_t dst_smem, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
 }
 template <bool F32>
 __global__ void __launch_bounds__(CS_TX * CS_RY) colsum_wide_kernel(const void* __restrict__ src, int ld, float* __restrict__ dst,
@@ -482,51 +485,47 @@ __global__ void __launch_bounds__(CS_TX * CS_RY) colsum_wide_kernel(const void* 
   pdl_launch_dependents();
   pdl_wait();
   constexpr int VEC = F32 ? 4 : 8;
-  __shared__ float sm[CS_TX * 8];
+  __shared__ uint4 ring[CS_STAGES][CS_TX * CS_RY];
   const int tx = threadIdx.x % CS_TX, ry = threadIdx.x / CS_TX;
   const int c = (blockIdx.x * CS_TX + tx) * VEC;
   const bool live = c < cols;
-  const int r0 = blockIdx.y * rows_per_block;
-  const int r1 = min(rows, r0 + rows_per_block);
+  const int r0 = blockIdx.y * rows_per_block + ry;
+  const int r1 = min(rows, blockIdx.y * rows_per_block + rows_per_block);
+  const int n = (live && r1 > r0) ? (r1 - r0 + CS_RY - 1) / CS_RY : 0;        // rows r0, r0 + CS_RY, ... < r1
   float acc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  if (live) {
-    const char* base = reinterpret_cast<const char*>(src) + size_t(c) * (F32 ? 4 : 2);
-    const size_t pitch = size_t(ld) * (F32 ? 4 : 2);
-    int r = r0 + ry;
-    const char* q = base + size_t(r) * pitch;
-    const size_t step = pitch * CS_RY;
-    for (; r + (CS_UNROLL - 1) * CS_RY < r1; r += CS_UNROLL * CS_RY) {
-      uint4 v[CS_UNROLL];
+  const size_t step = size_t(ld) * (F32 ? 4 : 2) * CS_RY;
+  const char* q = reinterpret_cast<const char*>(src) + size_t(c) * (F32 ? 4 : 2) + size_t(r0) * size_t(ld) * (F32 ? 4 : 2);
+  const uint32_t slot0 = static_cast<uint32_t>(__cvta_generic_to_shared(&ring[0][threadIdx.x]));
+  constexpr uint32_t SLOT_STRIDE = sizeof(uint4) * CS_TX * CS_RY;
 #pragma unroll
-      for (int u = 0; u < CS_UNROLL; ++u) { v[u] = ldg128_issue(q); q += step; }
-#pragma unroll
-      for (int u = 0; u < CS_UNROLL; ++u) {
-        if (F32) {
-          acc[0] += __uint_as_float(v[u].x); acc[1] += __uint_as_float(v[u].y);
-          acc[2] += __uint_as_float(v[u].z); acc[3] += __uint_as_float(v[u].w);
-        } else {
-          acc[0] += __uint_as_float(v[u].x << 16); acc[1] += __uint_as_float(v[u].x & 0xffff0000u);
-          acc[2] += __uint_as_float(v[u].y << 16); acc[3] += __uint_as_float(v[u].y & 0xffff0000u);
-          acc[4] += __uint_as_float(v[u].z << 16); acc[5] += __uint_as_float(v[u].z & 0xffff0000u);
-          acc[6] += __uint_as_float(v[u].w << 16); acc[7] += __uint_as_float(v[u].w & 0xffff0000u);
-        }
-      }
-    }
-    for (; r < r1; r += CS_RY, q += step) {
-      const uint4 v = ldg128_issue(q);
-      if (F32) {
-        acc[0] += __uint_as_float(v.x); acc[1] += __uint_as_float(v.y);
-        acc[2] += __uint_as_float(v.z); acc[3] += __uint_as_float(v.w);
-      } else {
-        acc[0] += __uint_as_float(v.x << 16); acc[1] += __uint_as_float(v.x & 0xffff0000u);
-        acc[2] += __uint_as_float(v.y << 16); acc[3] += __uint_as_float(v.y & 0xffff0000u);
-        acc[4] += __uint_as_float(v.z << 16); acc[5] += __uint_as_float(v.z & 0xffff0000u);
-        acc[6] += __uint_as_float(v.w << 16); acc[7] += __uint_as_float(v.w & 0xffff0000u);
-      }
-    }
+  for (int st = 0; st < CS_STAGES; ++st) {
+    if (st < n) cp_async_16(slot0 + st * SLOT_STRIDE, q + st * step);
+    cp_async_commit();
   }
+  q += CS_STAGES * step;
+  int st = 0;
+  for (int i = 0; i < n; ++i) {
+    cp_async_wait_group<CS_STAGES - 1>();                 // the group of row i has landed
+    const uint4 v = ring[st][threadIdx.x];
+    if (F32) {
+      acc[0] += __uint_as_float(v.x); acc[1] += __uint_as_float(v.y);
+      acc[2] += __uint_as_float(v.z); acc[3] += __uint_as_float(v.w);
+    } else {
+      acc[0] += __uint_as_float(v.x << 16); acc[1] += __uint_as_float(v.x & 0xffff0000u);
+      acc[2] += __uint_as_float(v.y << 16); acc[3] += __uint_as_float(v.y & 0xffff0000u);
+      acc[4] += __uint_as_float(v.z << 16); acc[5] += __uint_as_float(v.z & 0xffff0000u);
+      acc[6] += __uint_as_float(v.w << 16); acc[7] += __uint_as_float(v.w & 0xffff0000u);
+    }
+    if (i + CS_STAGES < n) cp_async_16(slot0 + st * SLOT_STRIDE, q);     // refill the slot just consumed
+    cp_async_commit();                                                   // one group per row keeps the count in step
+    q += step;
+    if (++st == CS_STAGES) st = 0;
+  }
+  cp_async_wait_group<0>();
+  __syncthreads();                                        // every thread is done with the ring: reuse it for the fold
+  float* sm = reinterpret_cast<float*>(&ring[0][0]);
   if (ry == 1) {
 #pragma unroll
     for (int i = 0; i < VEC; ++i) sm[i * CS_TX + tx] = acc[i];
@@ -544,8 +543,10 @@ int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, 
   static const bool narrow_only = getenv("GXA_COLSUM_NARROW") != nullptr;       // A/B switch (tools/)
   if (!narrow_only && cols % vec == 0 && ld % vec == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && rows >= 64) {
     const int gx = (cols / vec + CS_TX - 1) / CS_TX;
-    int gy = (num_sms() * 8 + gx - 1) / gx;
-    const int gy_max = (rows + CS_RY * CS_UNROLL - 1) / (CS_RY * CS_UNROLL);
+    static const int per_sm[2] = {[] { int nb = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, colsum_wide_kernel<false>, CS_TX * CS_RY, 0) == cudaSuccess && nb > 0 ? nb : 4; }(),
+                                  [] { int nb = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, colsum_wide_kernel<true>, CS_TX * CS_RY, 0) == cudaSuccess && nb > 0 ? nb : 4; }()};
+    int gy = num_sms() * per_sm[is_f32 ? 1 : 0] / gx;          // one resident wave (equal-sized blocks: no partial second wave)
+    const int gy_max = (rows + CS_RY * CS_STAGES - 1) / (CS_RY * CS_STAGES);
     if (gy > gy_max) gy = gy_max;
     if (gy < 1) gy = 1;
     const int rpb = (rows + gy - 1) / gy;

@@ -1,6 +1,7 @@
 """Per-kernel time inside a real bench step (CUPTI activity records via torch.profiler; kernels run back to back,
 warm caches -- unlike the serialised ncu launch list).  Not a bench line.
     python tools/step_profile.py [workload] [per_gpu_batch]
+LAYERS=n overrides the layer count; PLAIN=1 only runs a few steps (the command to put under `ncu --set full -k regex:...`).
 """
 import collections
 import os
@@ -17,6 +18,7 @@ import mocov2_whisper_flamingo_b200 as G  # noqa: E402
 wl = sys.argv[1] if len(sys.argv) > 1 else "whisper-medium-c3"
 D, H, layers, GB, Lq, Lk = bench.WORKLOADS[wl]
 B = int(sys.argv[2]) if len(sys.argv) > 2 else GB
+layers = int(os.environ.get("LAYERS", layers))
 torch.manual_seed(1234)
 model = G.GatedCrossModalFusion(D, H, layers, dropout=float(os.environ.get("DROPOUT", "0.0")))
 with torch.no_grad():
@@ -44,6 +46,9 @@ def step():
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+if os.environ.get("PLAIN"):
+    print("plain run done")
+    sys.exit(0)
 from torch.profiler import ProfilerActivity, profile  # noqa: E402
 
 N = 2
