@@ -72,3 +72,17 @@ print(f"{wl} B={B}: sum of kernel time {tot / N / 1e3:.2f} ms/step; wall span {(
       f"(gap = launch/idle)")
 for k, v_ in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"{v_[1] / N / 1e3:9.3f} ms {100 * v_[1] / tot:5.1f}%  n/step={v_[0] // N:5d}  avg={v_[1] / v_[0]:8.1f} us  {k}")
+
+# ---- idle gaps on the device timeline: intervals where no kernel of any stream is running
+iv = sorted((e.time_range.start, e.time_range.end, re.sub(r"\(.*", "", e.name)[:60]) for e in prof.events()
+            if e.device_type == torch.autograd.DeviceType.CUDA)
+gaps, cur_end, cur_name = [], iv[0][1], iv[0][2]
+for s_, t_, nm in iv[1:]:
+    if s_ > cur_end:
+        gaps.append((s_ - cur_end, cur_name, nm, cur_end - iv[0][0]))
+    if t_ > cur_end:
+        cur_end, cur_name = t_, nm
+idle = sum(g_[0] for g_ in gaps)
+print(f"device idle inside the {N}-step span: {idle / N / 1e3:.2f} ms/step in {len(gaps) // N} gaps/step; largest:")
+for g_ in sorted(gaps, key=lambda g_: -g_[0])[:14]:
+    print(f"  {g_[0]:8.1f} us at +{g_[3] / 1e3:8.2f} ms  after {g_[1]}  before {g_[2]}")
