@@ -22,22 +22,26 @@ constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_B_BYTES;
 // Epilogue width per fused epilogue: the GELU epilogues are latency-bound with 2 warps per scheduler (ncu: < 50 % issue
 // utilisation), so they get 16 epilogue warps (4 per TMEM lane quarter, 64 accumulator columns each) and give one smem
 // stage to the extra staging buffers; the others keep 8 warps and the 6-stage ring (long-K wgrad wants the depth).
-template <int EPI>
+//
+// STG = 0 is the configuration above.  A non-zero STG overrides the ring depth: a shallower ring leaves shared memory on
+// the SM for a co-resident CTA of an HBM-bound row-wise kernel -- experiment switch
+// GXA_WGRAD_STAGES for the fp32-accumulating (weight-gradient / dxa) GEMMs, off by default.
+template <int EPI, int STG = 0>
 struct G2Cfg {
   static constexpr int EPI_WARPS = (EPI == EPI_BIAS_GELU || EPI == EPI_GELU_BWD) ? 16 : 8;
   static constexpr int THREADS = (EPI_WARPS + 2) * 32;
   static constexpr int COLS_PER_WARP = 256 / (EPI_WARPS / 4);
-  static constexpr int STAGES = EPI_WARPS == 16 ? 5 : 6;
+  static constexpr int STAGES = STG != 0 ? STG : (EPI_WARPS == 16 ? 5 : 6);
   static constexpr int EPI_STAGE_BYTES = EPI_WARPS * 4096;
   static constexpr int SMEM_BYTES = STAGES * G2_STAGE_BYTES + EPI_STAGE_BYTES + 1024 + 256;
 };
 constexpr int G2_TMEM_COLS = 512;
 
-template <int EPI, bool A_MN, bool B_MN>
+template <int EPI, bool A_MN, bool B_MN, int STG = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G2Cfg<EPI>::THREADS, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmC, const GemmParams p, const int tma_c) {
-  constexpr int G2_EPI_WARPS = G2Cfg<EPI>::EPI_WARPS, G2_STAGES = G2Cfg<EPI>::STAGES;
+  constexpr int G2_EPI_WARPS = G2Cfg<EPI>::EPI_WARPS, G2_STAGES = G2Cfg<EPI, STG>::STAGES;
   constexpr int G2_COLS_PER_WARP = G2Cfg<EPI>::COLS_PER_WARP, G2_EPI_STAGE_BYTES = G2Cfg<EPI>::EPI_STAGE_BYTES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -226,7 +230,7 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t ou
 int make_tmap_f32_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
                      uint32_t box_outer);
 
-template <int EPI, bool A_MN, bool B_MN>
+template <int EPI, bool A_MN, bool B_MN, int STG = 0>
 static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stream) {
   CUtensorMap tmA, tmB;
   int e;
@@ -242,10 +246,10 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   if (EPI == EPI_F32 && (p.accumulate || p.k_splits > 1) && p.bias == nullptr &&
       make_tmap_f32_2d(&tmC, p.C, p.N, p.M, p.ldc, 32, 32) == 0)
     tma_c = 1;
-  auto kern = gemm_tc2_kernel<EPI, A_MN, B_MN>;
+  auto kern = gemm_tc2_kernel<EPI, A_MN, B_MN, STG>;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<EPI>::SMEM_BYTES) != cudaSuccess)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<EPI, STG>::SMEM_BYTES) != cudaSuccess)
       return GXA_ERR_CUDA;
     attr_set = true;
   }
@@ -253,14 +257,27 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
   const int total = num_m * num_n * p.k_splits;
   const int max_pairs = num_sms() / 2;
   const int pairs = total < max_pairs ? total : max_pairs;
-  const cudaError_t le = launch_pdl(kern, dim3(2 * pairs), dim3(G2Cfg<EPI>::THREADS), G2Cfg<EPI>::SMEM_BYTES, stream, tmA, tmB,
-                                    tmC, p, tma_c);
+  const cudaError_t le = launch_pdl(kern, dim3(2 * pairs), dim3(G2Cfg<EPI>::THREADS), G2Cfg<EPI, STG>::SMEM_BYTES, stream, tmA,
+                                    tmB, tmC, p, tma_c);
   count_launch();
   return le == cudaSuccess && cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA;
 }
 
+template <int STG>
+static int launch2_f32_shallow(const GemmOp& op, const GemmParams& p, cudaStream_t s) {
+  if (!op.a_mn && !op.b_mn) return launch2_inst<EPI_F32, false, false, STG>(op, p, s);
+  if (!op.a_mn && op.b_mn) return launch2_inst<EPI_F32, false, true, STG>(op, p, s);
+  if (op.a_mn && op.b_mn) return launch2_inst<EPI_F32, true, true, STG>(op, p, s);
+  return launch2_inst<EPI_F32, true, false, STG>(op, p, s);
+}
+
 template <int EPI>
 static int launch2_layout(const GemmOp& op, const GemmParams& p, cudaStream_t s) {
+  if constexpr (EPI == EPI_F32) {
+    static const int shallow = [] { const char* e = getenv("GXA_WGRAD_STAGES"); return e ? atoi(e) : 0; }();
+    if (shallow == 4) return launch2_f32_shallow<4>(op, p, s);
+    if (shallow == 5) return launch2_f32_shallow<5>(op, p, s);
+  }
   if (!op.a_mn && !op.b_mn) return launch2_inst<EPI, false, false>(op, p, s);
   if (!op.a_mn && op.b_mn) return launch2_inst<EPI, false, true>(op, p, s);
   if constexpr (EPI == EPI_F32) {
