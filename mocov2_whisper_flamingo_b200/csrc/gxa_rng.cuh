@@ -27,11 +27,17 @@ __host__ __device__ __forceinline__ uint32_t drop_mix(uint32_t ctr, uint32_t see
   return static_cast<uint32_t>(t >> 32) ^ static_cast<uint32_t>(t);
 }
 // keep decisions for the column pair (2*pair, 2*pair + 1):  u16 >= thresh, evaluated on the full word
+// -DGXA_DROP_DPX (GXA_NVCC_EXTRA, A/B experiment, same mask): both half-word compares in one VIMNMX.U16x2 with two
+// predicate outputs instead of a shift and two ISETP.
 __device__ __forceinline__ void drop_keep(const DropCfg& c, uint32_t ctr, bool& k0, bool& k1) {
   const uint32_t x = drop_mix(ctr, c.seed_lo, c.seed_hi);
+#ifdef GXA_DROP_DPX
+  __vibmax_u16x2(x, c.thresh | (c.thresh << 16), &k1, &k0);      // pred = (x.half >= thresh), high half first
+#else
   const uint32_t t = c.thresh << 16;
   k0 = (x << 16) >= t;
   k1 = x >= t;
+#endif
 }
 // multipliers (0 or cfg.scale) for the same pair
 __device__ __forceinline__ void drop_pair(const DropCfg& c, uint32_t ctr, float& m0, float& m1) {
