@@ -546,7 +546,7 @@ int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, 
     static const int per_sm[2] = {[] { int nb = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, colsum_wide_kernel<false>, CS_TX * CS_RY, 0) == cudaSuccess && nb > 0 ? nb : 4; }(),
                                   [] { int nb = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, colsum_wide_kernel<true>, CS_TX * CS_RY, 0) == cudaSuccess && nb > 0 ? nb : 4; }()};
     int gy = num_sms() * per_sm[is_f32 ? 1 : 0] / gx;          // one resident wave (equal-sized blocks: no partial second wave)
-    const int gy_max = (rows + CS_RY * CS_STAGES - 1) / (CS_RY * CS_STAGES);
+    const int gy_max = (rows + 2 * CS_RY * CS_STAGES - 1) / (2 * CS_RY * CS_STAGES);   // >= two ring turns per thread where the rows allow
     if (gy > gy_max) gy = gy_max;
     if (gy < 1) gy = 1;
     const int rpb = (rows + gy - 1) / gy;
