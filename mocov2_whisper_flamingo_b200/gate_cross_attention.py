@@ -31,6 +31,12 @@ logger = logging.getLogger(__name__)
 __all__ = ["LayerNorm", "GatedCrossAttentionBlock", "GatedCrossModalFusion", "set_default_precision"]
 
 
+def _log_shapes(enabled: bool, where: str, **tensors) -> None:
+    """``enable_logging=True`` (reference :29-35, :41-49, :61-72): tensor shapes at the module boundaries, INFO level."""
+    if enabled:
+        logger.info("%s: %s", where, ", ".join(f"{k}{tuple(t.shape)}" for k, t in tensors.items() if t is not None))
+
+
 class LayerNorm(nn.LayerNorm):
     """reference: models/gate_cross_attention.py:8-10 (fp32 statistics, result cast back to x.dtype)."""
 
@@ -44,14 +50,18 @@ class GatedCrossAttentionBlock(nn.Module):
     def __init__(self, d_model, n_heads, dropout=0.1, enable_logging=False):
         super().__init__()
         self.enable_logging = enable_logging
-        # registration order mirrors the reference (:16-27) so state_dict() ordering is identical
-        self.attn = nn.MultiheadAttention(embed_dim=d_model, num_heads=n_heads, dropout=dropout, batch_first=True)
-        self.attn_ln = LayerNorm(d_model)
-        self.ff_ln = LayerNorm(d_model)
-        self.attn_gate = nn.Parameter(torch.tensor([0.]))
-        self.ff_gate = nn.Parameter(torch.tensor([0.]))
-        n_mlp = d_model * 4
-        self.ff = nn.Sequential(nn.Linear(d_model, n_mlp), nn.GELU(), nn.Linear(n_mlp, d_model), nn.Dropout(dropout))
+        hidden = 4 * d_model            # the reference's FFN width (:21), independent of any fc_hidden_size
+        # Parameter containers only (their forward is never called), created and registered in the reference's order
+        # (:16-27): same default initialisation stream under torch.manual_seed and the same state_dict() ordering.
+        for name, holder in (
+                ("attn", nn.MultiheadAttention(d_model, n_heads, dropout=dropout, batch_first=True)),
+                ("attn_ln", LayerNorm(d_model)),
+                ("ff_ln", LayerNorm(d_model)),
+                ("attn_gate", nn.Parameter(torch.zeros(1))),
+                ("ff_gate", nn.Parameter(torch.zeros(1))),
+                ("ff", nn.Sequential(nn.Linear(d_model, hidden), nn.GELU(), nn.Linear(hidden, d_model),
+                                     nn.Dropout(dropout)))):
+            setattr(self, name, holder)
         self.d_model, self.n_heads, self.dropout = d_model, n_heads, dropout
         self._state = BlockState()
         self.precision: Optional[int] = None   # None: follow autocast / set_default_precision
@@ -64,15 +74,10 @@ class GatedCrossAttentionBlock(nn.Module):
                 self.ff[2].bias)
 
     def forward(self, x, xa=None, mask=None, _shared: Optional[StackShared] = None):
-        if self.enable_logging:
-            logger.info(f"GatedCrossAttentionBlock input x shape: {x.shape}")
-            if xa is not None:
-                logger.info(f"Cross attention input xa shape: {xa.shape}")
-            if mask is not None:
-                logger.info(f"Attention mask shape: {mask.shape}")
-        if xa is not None and xa.dim() == 4 and xa.size(1) == 1:
+        _log_shapes(self.enable_logging, "block in", x=x, xa=xa, mask=mask)
+        if xa is not None and xa.dim() == 4 and xa.size(1) == 1:          # [B, 1, Lk, D] visual memory (:35-36)
             xa = xa.squeeze(1)
-        if mask is not None and mask.dim() == 3 and mask.size(1) == 1:
+        if mask is not None and mask.dim() == 3 and mask.size(1) == 1:    # [B, 1, Lk] padding mask (:37-38)
             mask = mask.squeeze(1)
         # dropout (reference :16 attention probabilities, :26 after ff.2) is active in training mode only
         p_drop = float(self.dropout) if self.training else 0.0
@@ -80,8 +85,7 @@ class GatedCrossAttentionBlock(nn.Module):
         if shared is None:
             shared = StackShared(xa, mask if xa is not None else None, resolve_precision(self.precision))
         y = BlockFn.apply(x, xa, shared, self._state, self.n_heads, self, p_drop, *self._params())
-        if self.enable_logging:
-            logger.info(f"GatedCrossAttentionBlock output shape: {y.shape}")
+        _log_shapes(self.enable_logging, "block out", y=y)
         return y
 
 
@@ -107,18 +111,14 @@ class GatedCrossModalFusion(nn.Module):
             layer._state.key = None
 
     def forward(self, audio_features, video_features, audio_mask=None, video_mask=None):
-        if self.enable_logging:
-            logger.info(f"Fusion input audio_features shape: {audio_features.shape}")
-            logger.info(f"Fusion input video_features shape: {video_features.shape}")
+        _log_shapes(self.enable_logging, "fusion in", audio_features=audio_features, video_features=video_features)
         prec = resolve_precision(self.precision)
         x = LinearFn.apply(audio_features, self.audio_proj.weight, self.audio_proj.bias, prec)
         xa = LinearFn.apply(video_features, self.video_proj.weight, self.video_proj.bias, prec)
-        if self.enable_logging:
-            logger.info(f"After projection, x shape: {x.shape}, xa shape: {xa.shape}")
+        _log_shapes(self.enable_logging, "fusion projected", x=x, xa=xa)
         shared = StackShared(xa, video_mask, prec, grad_hook=self.grad_hook)
         for layer in self.layers:
             x = layer(x, xa, video_mask, _shared=shared)
         x = LayerNormFn.apply(x, self.ln_post.weight, self.ln_post.bias)
-        if self.enable_logging:
-            logger.info(f"Fusion output shape: {x.shape}")
+        _log_shapes(self.enable_logging, "fusion out", y=x)
         return x
