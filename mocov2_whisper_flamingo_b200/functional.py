@@ -12,7 +12,7 @@ from typing import Optional
 import torch
 
 from . import _lib
-from ._lib import BlockPtrs, Dims, GXA_PREC_BF16, GXA_PREC_FP32, PARAM_FIELDS, check
+from ._lib import BlockPtrs, Dims, GXA_PREC_BF16, GXA_PREC_FP32, check
 
 _default_precision: Optional[int] = None
 _workspaces: dict = {}

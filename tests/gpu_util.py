@@ -1,6 +1,5 @@
 """Helpers shared by the -m gpu tests: they call the product through its C ABI (ctypes) and compare
 against torch fp32/fp64 math or the oracle."""
-import ctypes as C
 
 import numpy as np
 import torch

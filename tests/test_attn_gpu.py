@@ -1,7 +1,6 @@
 """Masked-softmax attention kernels (gxa_attn_fwd / gxa_attn_bwd) vs fp32 torch math on the same bf16
 inputs.  Mask handling must be exact: padded keys contribute exactly nothing and get exactly zero grad.
 Tolerance 1.5e-2 relative (bf16 output rounding and bf16 probabilities in the PV product)."""
-import math
 
 import pytest
 import torch

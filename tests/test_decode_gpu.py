@@ -1,7 +1,6 @@
 """Decode-time path (BASELINE config 5): per-layer cached K|V + per-step query rows must reproduce the
 stack's forward on those rows (the reference itself has no decode loop; its block called with x[:, t:t+1] and the full
 visual memory is the oracle)."""
-import numpy as np
 import pytest
 import torch
 

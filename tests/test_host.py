@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import GOLDEN, ROOT
+from conftest import ROOT
 from oracle import gxa_oracle as O
 import mocov2_whisper_flamingo_b200 as G
 from mocov2_whisper_flamingo_b200 import _lib

@@ -1,6 +1,5 @@
 """Top source lines by warp-stall samples from an ncu report captured with --import-source on (-lineinfo build).
     python tools/ncu_hot.py gpurun_out/x.ncu-rep [N]"""
-import collections
 import csv
 import subprocess
 import sys
