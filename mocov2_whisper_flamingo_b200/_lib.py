@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgxa_b200.so")
+# GXA_LIB: another in-tree build of the same sources (A/B variants made with GXA_BUILD_VARIANT, see build.py)
+LIB_PATH = os.environ.get("GXA_LIB") or os.path.join(_HERE, "libgxa_b200.so")
 
 GXA_PREC_BF16, GXA_PREC_FP32 = 0, 1
 EPI_BF16, EPI_F32, EPI_GATE_RES, EPI_BIAS_GELU, EPI_GELU_BWD = 0, 1, 2, 3, 4

@@ -14,8 +14,11 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(HERE, "build")
-LIB = os.path.join(HERE, "libgxa_b200.so")
+# GXA_BUILD_VARIANT=name (with GXA_NVCC_EXTRA=-D...) builds libgxa_b200.<name>.so beside the product library, for A/B runs
+# selected with GXA_LIB=<path>; the product library and its object directory are untouched.
+_VARIANT = os.environ.get("GXA_BUILD_VARIANT", "")
+OBJ = os.path.join(HERE, "build" + ("_" + _VARIANT if _VARIANT else ""))
+LIB = os.path.join(HERE, "libgxa_b200." + _VARIANT + ".so" if _VARIANT else "libgxa_b200.so")
 SOURCES = ["gxa_gemm.cu", "gxa_gemm2.cu", "gxa_rowwise.cu", "gxa_attn.cu", "gxa_attn_tc.cu", "gxa_attn_bwd_tc.cu", "gxa_attn_f32.cu", "gxa_api.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
