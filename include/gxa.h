@@ -87,6 +87,14 @@ long long gxa_launch_count(void);
  * whole device; returns the previous limit. */
 int gxa_set_sm_limit(int n_sms);
 
+/* Host-side evaluation of the training-mode dropout masks (reference: nn.MultiheadAttention(dropout=p) on the attention
+ * probabilities and nn.Dropout(p) after ff.2, models/gate_cross_attention.py:16, :26).  The kernels never store a mask:
+ * forward and backward evaluate one counter-based function of (seed, element) (csrc/gxa_rng.cuh); this entry point
+ * evaluates the SAME compiled function on the host for a [rows, cols] matrix, so a caller (or a test) can reproduce the
+ * mask a call used.  site: 1 = attention probabilities (rows = B*H*Lq, cols = Lk), 2 = FFN output (rows = B*Lq,
+ * cols = D).  out[r*cols + c] = 0 where dropped, 1/(1-p) where kept.  No device work. */
+int gxa_dropout_multipliers_host(float p_drop, uint64_t seed, int site, int rows, int cols, float* out);
+
 /* ---- sizes ------------------------------------------------------------------------ */
 /* bytes of the per-layer bf16 (or split) weight cache written by gxa_block_prepare_weights */
 size_t gxa_block_wcache_bytes(const gxa_dims* d);

@@ -40,6 +40,7 @@ SIGNATURES = {
     "gxa_version": (C.c_char_p, []),
     "gxa_last_cuda_error": (C.c_char_p, []),
     "gxa_launch_count": (C.c_longlong, []),
+    "gxa_dropout_multipliers_host": (_i, [C.c_float, C.c_uint64, _i, _i, _i, _vp]),
     "gxa_set_sm_limit": (C.c_int, [C.c_int]),
     "gxa_block_wcache_bytes": (_sz, [_dp]),
     "gxa_block_saved_bytes": (_sz, [_dp]),

@@ -432,6 +432,20 @@ int gxa_query_caps(int* sm_count, int* cc_major, int* cc_minor) {
 const char* gxa_version(void) { return "gxa-b200 0.1 (sm_100a; tcgen05+TMA GEMMs)"; }
 const char* gxa_last_cuda_error(void) { return g_err; }
 long long gxa_launch_count(void) { return g_launches.load(); }
+int gxa_dropout_multipliers_host(float p_drop, uint64_t seed, int site, int rows, int cols, float* out) {
+  if (!out || rows < 0 || cols < 0) return GXA_ERR_ARG;
+  if (!(p_drop >= 0.f && p_drop < 1.f) || (site != int(kDropStreamAttn) && site != int(kDropStreamFfn))) return GXA_ERR_ARG;
+  const DropCfg c = make_drop_cfg(p_drop, seed, uint32_t(site));
+  const uint32_t half = uint32_t(cols + 1) >> 1, t = c.thresh << 16;
+  for (int r = 0; r < rows; ++r)
+    for (int col = 0; col < cols; ++col) {
+      if (c.thresh == 0) { out[size_t(r) * cols + col] = 1.f; continue; }
+      const uint32_t x = drop_mix(uint32_t(r) * half + (uint32_t(col) >> 1), c.seed_lo, c.seed_hi);   // gxa_rng.cuh
+      const bool keep = (col & 1) ? x >= t : (x << 16) >= t;
+      out[size_t(r) * cols + col] = keep ? c.scale : 0.f;
+    }
+  return 0;
+}
 int gxa_set_sm_limit(int n_sms) { return g_sm_limit.exchange(n_sms < 0 ? 0 : n_sms); }
 
 size_t gxa_block_wcache_bytes(const gxa_dims* d) {

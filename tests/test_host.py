@@ -59,7 +59,7 @@ def test_state_dict_layout_and_strict_load():
 def test_init_matches_reference_defaults():
     blk = G.GatedCrossAttentionBlock(128, 2)
     assert blk.attn_gate.item() == 0.0 and blk.ff_gate.item() == 0.0     # identity at init (A.1 M6)
-    assert float(blk.attn.in_proj_bias.abs().max()) == 0.0 and float(blk.attn.out_proj.bias.abs().max()) == 0.0
+    assert float(blk.attn.in_proj_bias.detach().abs().max()) == 0.0 and float(blk.attn.out_proj.bias.detach().abs().max()) == 0.0
     assert tuple(blk.ff[0].weight.shape) == (512, 128)                   # hidden = 4 * d_model
 
 
@@ -120,3 +120,25 @@ def test_balanced_shards_even_out_frame_counts():
             assert max(tot) / (sum(tot) / world) < 1.05 < 1.3 < max(contiguous) / (sum(contiguous) / world)
     assert balanced_shards([5, 5, 5], 2) == [[0], [1, 2]]                              # serpentine; ties keep index order
     assert balanced_shards([], 3) == [[], [], []]
+
+
+def test_dropout_restatement_is_bit_identical_to_the_compiled_mask_function():
+    """tests/dropout_ref.py (what the -m gpu parity tests feed the oracle) against the mask function the kernels are
+    compiled from (csrc/gxa_rng.cuh), evaluated on the host through gxa_dropout_multipliers_host: every multiplier equal."""
+    import sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    import numpy as np
+    import dropout_ref as DR
+    L = _lib.lib()
+    for rows, cols, p, seed, site in [(96, 750, 0.1, 0x1234ABCD5678EF01, DR.STREAM_ATTN),
+                                      (37, 751, 0.1, 0xFFFFFFFFFFFFFFFF, DR.STREAM_ATTN),      # odd column count
+                                      (64, 1024, 0.25, 7, DR.STREAM_FFN),
+                                      (5, 9, 0.999, 3, DR.STREAM_FFN),
+                                      (3, 8, 0.0, 11, DR.STREAM_ATTN)]:
+        out = np.empty((rows, cols), np.float32)
+        rc = L.gxa_dropout_multipliers_host(p, seed, site, rows, cols, out.ctypes.data)
+        assert rc == 0
+        ref = DR.multipliers(rows, cols, p, seed, site)
+        assert np.array_equal(out, ref), (rows, cols, p, site)
+    assert L.gxa_dropout_multipliers_host(1.0, 1, 1, 1, 1, np.empty(1, np.float32).ctypes.data) != 0      # p must be < 1
+    assert L.gxa_dropout_multipliers_host(0.1, 1, 3, 1, 1, np.empty(1, np.float32).ctypes.data) != 0      # unknown site
