@@ -139,7 +139,6 @@ static int check_dims(const gxa_dims* d) {
   if (d->D != d->H * 64 || d->D % 128 != 0) return GXA_ERR_SHAPE;
   if (d->precision != GXA_PREC_BF16 && d->precision != GXA_PREC_FP32) return GXA_ERR_UNSUPPORTED;
   if (!(d->p_drop >= 0.f && d->p_drop < 1.f)) return GXA_ERR_ARG;
-  if (d->p_drop > 0.f && d->precision != GXA_PREC_BF16) return GXA_ERR_UNSUPPORTED;   // dropout: bf16 training mode only
   return 0;
 }
 
@@ -294,7 +293,8 @@ static int block_fwd_f32(const gxa_dims& d, const gxa_block_params& p, const flo
     GXA_TRY(gemm_f32(S.h, D, false, p.in_proj_w, D, false, M, D, D, S.q, D, p.in_proj_b, 0, Wk.A3, Wk.B3, s));
     GXA_TRY(gemm_f32(xa, D, false, p.in_proj_w + size_t(D) * D, D, false, Mk, 2 * D, D, S.kv, 2 * D, p.in_proj_b + D, 0,
                      Wk.A3, Wk.B3, s));
-    GXA_TRY(attn_fwd_f32(S.q, D, S.kv, S.kv + D, 2 * D, mask, S.ctx, D, S.P, d.B, d.H, d.Lq, d.Lk, s));
+    GXA_TRY(attn_fwd_f32(S.q, D, S.kv, S.kv + D, 2 * D, mask, S.ctx, D, S.P, d.B, d.H, d.Lq, d.Lk, s,
+                         make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
     GXA_TRY(gemm_f32(S.ctx, D, false, p.out_proj_w, D, false, M, D, D, S.o, D, p.out_proj_b, 0, Wk.A3, Wk.B3, s));
     GXA_TRY(gate_res_f32(x, S.o, p.attn_gate, S.x1, size_t(M) * D, s));
     x1 = S.x1;
@@ -303,7 +303,7 @@ static int block_fwd_f32(const gxa_dims& d, const gxa_block_params& p, const flo
   GXA_TRY(gemm_f32(S.h2, D, false, p.ff0_w, D, false, M, 4 * D, D, S.u, 4 * D, p.ff0_b, 0, Wk.A3, Wk.B3, s));
   GXA_TRY(gelu_f32(S.u, S.a, size_t(M) * 4 * D, s));
   GXA_TRY(gemm_f32(S.a, 4 * D, false, p.ff2_w, 4 * D, false, M, D, 4 * D, S.f, D, p.ff2_b, 0, Wk.A3, Wk.B3, s));
-  GXA_TRY(gate_res_f32(x1, S.f, p.ff_gate, y, size_t(M) * D, s));
+  GXA_TRY(gate_res_f32(x1, S.f, p.ff_gate, y, size_t(M) * D, s, D, make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn)));   // S.f = dropout(f)
   return 0;
 }
 
@@ -378,7 +378,8 @@ static int block_bwd_f32(const gxa_dims& d, const gxa_block_params& p, const flo
   const float* xa = reinterpret_cast<const float*>(xa_op);
   if (cudaMemsetAsync(Wk.gacc, 0, 64 * sizeof(float), s) != cudaSuccess) return fail(GXA_ERR_CUDA);
   const float* x1 = d.has_xa ? S.x1 : x;
-  GXA_TRY(gate_bwd(dy, S.f, 1, p.ff_gate, Wk.gacc + 1, Wk.df, 1, g.ff2_b, M, D, s));
+  GXA_TRY(gate_bwd(dy, S.f, 1, p.ff_gate, Wk.gacc + 1, Wk.df, 1, g.ff2_b, M, D, s,
+                   make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn)));
   GXA_TRY(gemm_f32(Wk.df, D, false, p.ff2_w, 4 * D, true, M, 4 * D, D, Wk.da, 4 * D, nullptr, 0, Wk.A3, Wk.B3, s));
   GXA_TRY(gelu_bwd_f32(Wk.da, S.u, Wk.du, size_t(M) * 4 * D, s));
   GXA_TRY(gemm_f32(Wk.df, D, true, S.a, 4 * D, true, D, 4 * D, M, g.ff2_w, 4 * D, nullptr, 1, Wk.A3, Wk.B3, s));
@@ -397,7 +398,7 @@ static int block_bwd_f32(const gxa_dims& d, const gxa_block_params& p, const flo
   GXA_TRY(gemm_f32(Wk.dob, D, false, p.out_proj_w, D, true, M, D, D, Wk.dctx, D, nullptr, 0, Wk.A3, Wk.B3, s));
   GXA_TRY(gemm_f32(Wk.dob, D, true, S.ctx, D, true, D, D, M, g.out_proj_w, D, nullptr, 1, Wk.A3, Wk.B3, s));
   GXA_TRY(attn_bwd_f32(S.q, D, S.kv, S.kv + D, 2 * D, Wk.dctx, D, S.P, Wk.dS, Wk.dq, D, Wk.dkv, Wk.dkv + D, 2 * D, d.B,
-                       d.H, d.Lq, d.Lk, s));
+                       d.H, d.Lq, d.Lk, s, make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
   GXA_TRY(colsum(Wk.dq, 1, D, g.in_proj_b, M, D, s));
   GXA_TRY(colsum(Wk.dkv + D, 1, 2 * D, g.in_proj_b + 2 * D, Mk, D, s));      // d(bv); d(bk) == 0 (see the bf16 path)
   GXA_TRY(gemm_f32(Wk.dq, D, true, S.h, D, true, D, D, M, g.in_proj_w, D, nullptr, 1, Wk.A3, Wk.B3, s));

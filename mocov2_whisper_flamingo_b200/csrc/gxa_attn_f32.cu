@@ -27,10 +27,18 @@ __device__ __forceinline__ float dot64(const float* a /*smem*/, const float* __r
   return s;
 }
 
+// dropout multiplier (0 or 1/(1-p)) of probability (row, key): the same function of (seed, element) as the bf16 kernels
+__device__ __forceinline__ float drop_mult(const DropCfg& c, uint32_t drop_row, int key) {
+  if (c.thresh == 0) return 1.f;
+  float m0, m1;
+  drop_pair(c, drop_row + (static_cast<uint32_t>(key) >> 1), m0, m1);
+  return (key & 1) ? m1 : m0;
+}
+
 __global__ void __launch_bounds__(128)
 attn_fwd_f32_kernel(const float* __restrict__ q, int ldq, const float* __restrict__ k, const float* __restrict__ v,
                     int ldkv, const uint8_t* __restrict__ mask, float* __restrict__ ctx, int ldc, float* __restrict__ P,
-                    int B, int H, int Lq, int Lk) {
+                    int B, int H, int Lq, int Lk, const DropCfg drop) {
   __shared__ float sq[4][HD];
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * 4 + w;   // (b, h, qi)
@@ -62,8 +70,9 @@ attn_fwd_f32_kernel(const float* __restrict__ q, int ldq, const float* __restric
   for (int j = l; j < Lk; j += 32) pr[j] *= inv;
   __syncwarp();
   float a0 = 0.f, a1 = 0.f;
+  const uint32_t drop_row = static_cast<uint32_t>(row) * static_cast<uint32_t>((Lk + 1) >> 1);   // gxa_rng.cuh counter
   for (int j = 0; j < Lk; ++j) {
-    const float p = pr[j];
+    const float p = pr[j] * drop_mult(drop, drop_row, j);       // P stays undropped in memory (the backward needs both)
     float2 vv = *reinterpret_cast<const float2*>(vb + size_t(j) * ldkv + 2 * l);
     a0 += p * vv.x;
     a1 += p * vv.y;
@@ -75,7 +84,7 @@ attn_fwd_f32_kernel(const float* __restrict__ q, int ldq, const float* __restric
 __global__ void __launch_bounds__(128)
 attn_bwd_f32_q_kernel(const float* __restrict__ k, const float* __restrict__ v, int ldkv,
                       const float* __restrict__ dctx, int ldc, const float* __restrict__ P, float* __restrict__ dS,
-                      float* __restrict__ dq, int lddq, int B, int H, int Lq, int Lk) {
+                      float* __restrict__ dq, int lddq, int B, int H, int Lq, int Lk, const DropCfg drop) {
   __shared__ float sd[4][HD];
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * 4 + w;
@@ -90,9 +99,11 @@ attn_bwd_f32_q_kernel(const float* __restrict__ k, const float* __restrict__ v, 
   const float* pr = P + size_t(row) * Lk;
   float* ds = dS + size_t(row) * Lk;
   float delta = 0.f;
+  const uint32_t drop_row = static_cast<uint32_t>(row) * static_cast<uint32_t>((Lk + 1) >> 1);
   for (int j = l; j < Lk; j += 32) {
     const float p = pr[j];
-    const float dp = p != 0.f ? dot64(sd[w], vb + size_t(j) * ldkv) : 0.f;
+    // forward: ctx = (m * P) V  =>  dP = m * (dO V^T);  delta = rowsum(P * dP) = rowsum(dO * ctx)
+    const float dp = p != 0.f ? drop_mult(drop, drop_row, j) * dot64(sd[w], vb + size_t(j) * ldkv) : 0.f;
     ds[j] = dp;
     delta += p * dp;
   }
@@ -113,7 +124,7 @@ attn_bwd_f32_q_kernel(const float* __restrict__ k, const float* __restrict__ v, 
 __global__ void __launch_bounds__(128)
 attn_bwd_f32_k_kernel(const float* __restrict__ q, int ldq, const float* __restrict__ dctx, int ldc,
                       const float* __restrict__ P, const float* __restrict__ dS, float* __restrict__ dk,
-                      float* __restrict__ dv, int lddkv, int B, int H, int Lq, int Lk) {
+                      float* __restrict__ dv, int lddkv, int B, int H, int Lq, int Lk, const DropCfg drop) {
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * 4 + w;   // (b, h, j)
   if (row >= (long long)B * H * Lk) return;
@@ -123,8 +134,11 @@ attn_bwd_f32_k_kernel(const float* __restrict__ q, int ldq, const float* __restr
   const float* pb = P + (size_t(b) * H + h) * Lq * Lk + j;
   const float* sb = dS + (size_t(b) * H + h) * Lq * Lk + j;
   float k0 = 0.f, k1 = 0.f, v0 = 0.f, v1 = 0.f;
+  const uint32_t half = static_cast<uint32_t>((Lk + 1) >> 1);
+  const uint32_t drop_row0 = static_cast<uint32_t>((size_t(b) * H + h) * Lq) * half;
   for (int i = 0; i < Lq; ++i) {
-    const float p = pb[size_t(i) * Lk], g = sb[size_t(i) * Lk];
+    const float p = pb[size_t(i) * Lk] * drop_mult(drop, drop_row0 + static_cast<uint32_t>(i) * half, j);   // dV sees m * P
+    const float g = sb[size_t(i) * Lk];
     float2 qq = *reinterpret_cast<const float2*>(qb + size_t(i) * ldq);
     float2 dd = *reinterpret_cast<const float2*>(db + size_t(i) * ldc);
     k0 += g * qq.x; k1 += g * qq.y;
@@ -138,19 +152,19 @@ attn_bwd_f32_k_kernel(const float* __restrict__ q, int ldq, const float* __restr
 static inline int chk32() { count_launch(); return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA; }
 
 int attn_fwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const uint8_t* mask, float* ctx,
-                 int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s) {
+                 int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s, DropCfg drop) {
   const long long rows = (long long)B * H * Lq;
-  attn_fwd_f32_kernel<<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(q, ldq, k, v, ldkv, mask, ctx, ldc, P, B, H, Lq, Lk);
+  attn_fwd_f32_kernel<<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(q, ldq, k, v, ldkv, mask, ctx, ldc, P, B, H, Lq, Lk, drop);
   return chk32();
 }
 int attn_bwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const float* dctx, int ldc,
                  const float* P, float* dS, float* dq, int lddq, float* dk, float* dv, int lddkv, int B, int H, int Lq,
-                 int Lk, cudaStream_t s) {
+                 int Lk, cudaStream_t s, DropCfg drop) {
   const long long rows = (long long)B * H * Lq;
-  attn_bwd_f32_q_kernel<<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(k, v, ldkv, dctx, ldc, P, dS, dq, lddq, B, H, Lq, Lk);
+  attn_bwd_f32_q_kernel<<<(unsigned)((rows + 3) / 4), 128, 0, s>>>(k, v, ldkv, dctx, ldc, P, dS, dq, lddq, B, H, Lq, Lk, drop);
   if (int e = chk32()) return e;
   const long long krows = (long long)B * H * Lk;
-  attn_bwd_f32_k_kernel<<<(unsigned)((krows + 3) / 4), 128, 0, s>>>(q, ldq, dctx, ldc, P, dS, dk, dv, lddkv, B, H, Lq, Lk);
+  attn_bwd_f32_k_kernel<<<(unsigned)((krows + 3) / 4), 128, 0, s>>>(q, ldq, dctx, ldc, P, dS, dk, dv, lddkv, B, H, Lq, Lk, drop);
   return chk32();
 }
 

@@ -88,7 +88,9 @@ int split3(const float* src, int ld, void* dst, int rows, int cols, int pattern,
 int mask_kv_end(const uint8_t* mask, int* kv_end, int B, int Lk, cudaStream_t s);
 int gelu_f32(const float* u, float* a, size_t n, cudaStream_t s);
 int gelu_bwd_f32(const float* da, const float* u, float* du, size_t n, cudaStream_t s);
-int gate_res_f32(const float* x, const float* o, const float* gate, float* y, size_t n, cudaStream_t s);
+// y = x + tanh(gate) * o;  with dropout (nn.Dropout after ff.2, fp32 mode): o <- dropout(o) in place first (cols = row width)
+int gate_res_f32(const float* x, float* o, const float* gate, float* y, size_t n, cudaStream_t s, int cols = 0,
+                 DropCfg drop = DropCfg{0, 1.f, 0, 0});
 int add_inplace_f32(float* dst, const float* src, size_t n, cudaStream_t s);
 
 // ---- attention (gxa_attn.cu: bf16 tensor-core path; gxa_attn_f32.cu: fp32 accuracy path)
@@ -102,9 +104,9 @@ int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
                   DropCfg drop = DropCfg{0, 1.f, 0, 0});
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq);
 int attn_fwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const uint8_t* mask, float* ctx,
-                 int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s);
+                 int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s, DropCfg drop = DropCfg{0, 1.f, 0, 0});
 int attn_bwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const float* dctx, int ldc,
                  const float* P, float* dS, float* dq, int lddq, float* dk, float* dv, int lddkv, int B, int H, int Lq,
-                 int Lk, cudaStream_t s);
+                 int Lk, cudaStream_t s, DropCfg drop = DropCfg{0, 1.f, 0, 0});
 
 }  // namespace gxa

@@ -690,11 +690,21 @@ __global__ void gelu_bwd_f32_kernel(const float* __restrict__ da, const float* _
     du[i] = da[i] * (cdf + v * pdf);
   }
 }
-__global__ void gate_res_f32_kernel(const float* __restrict__ x, const float* __restrict__ o,
-                                    const float* __restrict__ gate, float* __restrict__ y, size_t n) {
+__global__ void gate_res_f32_kernel(const float* __restrict__ x, float* __restrict__ o,
+                                    const float* __restrict__ gate, float* __restrict__ y, size_t n, int cols,
+                                    const DropCfg drop) {
   const float t = tanhf(__ldg(gate));
-  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
-    y[i] = x[i] + t * o[i];
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    float ov = o[i];
+    if (drop.thresh != 0) {      // same (row, column pair) counter as the bf16 FFN2 epilogue and gate_bwd_kernel
+      const uint32_t row = static_cast<uint32_t>(i / cols), c = static_cast<uint32_t>(i % cols);
+      float m0, m1;
+      drop_pair(drop, row * static_cast<uint32_t>(cols >> 1) + (c >> 1), m0, m1);
+      ov *= (c & 1) ? m1 : m0;
+      o[i] = ov;
+    }
+    y[i] = x[i] + t * ov;
+  }
 }
 __global__ void add_inplace_kernel(float* __restrict__ dst, const float* __restrict__ src, size_t n) {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
@@ -710,9 +720,10 @@ int gelu_bwd_f32(const float* da, const float* u, float* du, size_t n, cudaStrea
   gelu_bwd_f32_kernel<<<ew_grid(n), 256, 0, s>>>(da, u, du, n);
   return check_launch();
 }
-int gate_res_f32(const float* x, const float* o, const float* gate, float* y, size_t n, cudaStream_t s) {
+int gate_res_f32(const float* x, float* o, const float* gate, float* y, size_t n, cudaStream_t s, int cols, DropCfg drop) {
   if (!n) return 0;
-  gate_res_f32_kernel<<<ew_grid(n), 256, 0, s>>>(x, o, gate, y, n);
+  if (drop.thresh != 0 && cols <= 0) return GXA_ERR_ARG;
+  gate_res_f32_kernel<<<ew_grid(n), 256, 0, s>>>(x, o, gate, y, n, cols > 0 ? cols : 1, drop);
   return check_launch();
 }
 int add_inplace_f32(float* dst, const float* src, size_t n, cudaStream_t s) {

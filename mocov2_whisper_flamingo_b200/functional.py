@@ -107,6 +107,7 @@ class StackShared:
         self.kv_end = None
         self.xa_op = None
         self.dxa = None
+        self.dxa_wanted = False      # some layer saw xa.requires_grad
         self.first_token = None      # identity of the first block call (its backward runs last)
         self.grad_hook = grad_hook   # callable(layer_token, flat_bucket) -> None (data-parallel all-reduce)
         L = _lib.lib()
@@ -146,13 +147,24 @@ class BlockFn(torch.autograd.Function):
     def forward(ctx, x, xa, shared: StackShared, state: BlockState, n_heads: int, token, p_drop: float, *params):
         L = _lib.lib()
         _require_cuda(x, "x")
+        if x.dim() != 3:
+            raise AssertionError(f"query should be batched 3D tensor [B, Lq, D] but received {x.dim()}-D query tensor")
         B, Lq, D = x.shape
         xf = _f32c(x)
         has_xa = xa is not None
+        if has_xa:
+            # the checks F.multi_head_attention_forward makes on key / value (torch/nn/functional.py:6229-6241, :6478)
+            _require_cuda(xa, "xa")
+            if xa.dim() != 3:
+                raise AssertionError(f"key and value should be 3D tensors [B, Lk, D] but received a {xa.dim()}-D tensor")
+            if xa.device != x.device:
+                raise RuntimeError(f"gxa_b200: x is on {x.device} but xa is on {xa.device}")
+            if xa.shape[0] != B:
+                raise AssertionError(f"key / value batch size {xa.shape[0]} does not match the query batch size {B}")
+            if xa.shape[2] != D:
+                raise RuntimeError(f"key / value feature width {xa.shape[2]} does not match embed_dim {D} "
+                                   "(mat1 and mat2 shapes cannot be multiplied)")
         Lk = xa.shape[1] if has_xa else 0
-        if p_drop > 0.0 and shared.precision != GXA_PREC_BF16:
-            raise NotImplementedError("gxa_b200: training-mode dropout is implemented for the bf16 (autocast) precision "
-                                      "only; use torch.autocast / set_default_precision('bf16'), dropout=0.0 or .eval()")
         dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa, p_drop, next_dropout_seed() if p_drop > 0.0 else 0)
         pd = [p.detach() for p in params]
         for p in pd:
@@ -162,7 +174,6 @@ class BlockFn(torch.autograd.Function):
         pp = BlockPtrs(*[p.data_ptr() for p in pd])
         wcache = state.refresh(dims, pd, pp)
         if has_xa and shared.xa_op is None:
-            _require_cuda(xa, "xa")
             n = L.gxa_xa_operand_bytes(C.byref(dims))
             shared.xa_op = torch.empty(n, dtype=torch.uint8, device=x.device)
             check(L.gxa_xa_prepare(C.byref(dims), _f32c(xa).data_ptr(), shared.xa_op.data_ptr(), _stream()),
@@ -180,16 +191,21 @@ class BlockFn(torch.autograd.Function):
                               _p(shared.mask_u8), _p(shared.kv_end), y.data_ptr(), saved.data_ptr(), ws.data_ptr(),
                               _stream()), "gxa_block_fwd")
         ctx.dims, ctx.shared, ctx.state, ctx.token = dims, shared, state, token
-        ctx.saved_buf, ctx.wcache = saved, wcache
+        ctx.wcache = wcache
         ctx.xa_shape = tuple(xa.shape) if has_xa else None
+        ctx.xa_needs_grad = bool(has_xa and ctx.needs_input_grad[1])
+        if ctx.xa_needs_grad:
+            shared.dxa_wanted = True
         ctx.x_dtype = x.dtype
-        ctx.save_for_backward(xf, *pd)
+        # the activation stash is an ordinary saved tensor: autograd releases it after this node's backward
+        # (layer by layer during the step) and keeps it under retain_graph=True
+        ctx.save_for_backward(xf, saved, *pd)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         L = _lib.lib()
-        xf, *pd = ctx.saved_tensors
+        xf, saved, *pd = ctx.saved_tensors
         dims, shared = ctx.dims, ctx.shared
         D = dims.D
         dyf = _f32c(dy)
@@ -200,23 +216,25 @@ class BlockFn(torch.autograd.Function):
         gp = BlockPtrs(*[v.data_ptr() for v in views])
         dx = torch.empty_like(xf)
         dxa_ptr = None
-        if dims.has_xa:
+        if dims.has_xa and shared.dxa_wanted:      # xa without requires_grad: the d(xa) GEMM is not run at all
             if shared.dxa is None:
                 shared.dxa = torch.zeros(ctx.xa_shape, dtype=torch.float32, device=xf.device)
             dxa_ptr = shared.dxa.data_ptr()
         ws = workspace(L.gxa_block_workspace_bytes(C.byref(dims)), xf.device)
         check(L.gxa_block_bwd(C.byref(dims), C.byref(pp), ctx.wcache.data_ptr(), xf.data_ptr(), _p(shared.xa_op),
-                              _p(shared.mask_u8), _p(shared.kv_end), ctx.saved_buf.data_ptr(), dyf.data_ptr(),
+                              _p(shared.mask_u8), _p(shared.kv_end), saved.data_ptr(), dyf.data_ptr(),
                               dx.data_ptr(), dxa_ptr, C.byref(gp), ws.data_ptr(), _stream()), "gxa_block_bwd")
-        ctx.saved_buf = None
+        owned = False
         if shared.grad_hook is not None:
-            shared.grad_hook(ctx.token, bucket)
+            # data-parallel hook (parallel.py): installs the layer's gradients as p.grad itself and orders the all-reduce;
+            # autograd must then not see them (AccumulateGrad would touch the bucket while NCCL reduces it in place)
+            owned = bool(shared.grad_hook(ctx.token, bucket))
         dxa = None
-        if dims.has_xa and ctx.token is shared.first_token:
+        if dims.has_xa and shared.dxa_wanted and ctx.token is shared.first_token:
             dxa = shared.dxa          # every layer has accumulated into it by now
             shared.dxa = None
-        grads = list(views)
-        if not dims.has_xa:           # attention parameters did not take part (reference: grad None)
+        grads = [None] * len(views) if owned else list(views)
+        if not dims.has_xa and not owned:           # attention parameters did not take part (reference: grad None)
             for i in (0, 2, 3, 4, 5, 6, 7):
                 grads[i] = None
         return (dx.to(ctx.x_dtype) if ctx.x_dtype != torch.float32 else dx, dxa, None, None, None, None, None, *grads)

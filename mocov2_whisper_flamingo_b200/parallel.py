@@ -7,22 +7,37 @@ stream (ordered after the layer's kernels by an event), so the NVLink/NVSwitch t
 overlaps the backward kernels of layers i-1 .. 0.  ``finish()`` makes the compute stream wait for the
 communication stream and reduces the few stack-level parameters (audio_proj, video_proj, ln_post).
 
-SM budget: the NCCL kernel keeps its CTAs (NCCL_MAX_CTAS, default taken as 16) resident while a bucket is in flight.
-The library's persistent kernels partition their work statically over the CTAs they launch, so a CTA that has to wait
-for an SM held by NCCL doubles that kernel's time.  From the first bucket until ``finish()`` the library is therefore
-told to size its grids for ``SMs - comm_sms`` (``gxa_set_sm_limit``); forward and the first backward layer use the
-whole device.  Measured at c3, 8 GPUs: see DESIGN.md section 6.
+Ownership of the layer gradients.  While a DataParallelGrads is attached, ``BlockFn.backward`` does NOT hand the
+parameter gradients of a layer to autograd (it returns None for them): the hook below installs them as ``p.grad``
+itself.  Autograd's AccumulateGrad would otherwise run ``p.grad += view`` on the compute stream whenever a gradient is
+already present (gradient accumulation -- the reference trains with accumulate_grad_batches = 4, config.py:42 -- or
+``zero_grad(set_to_none=False)``), reading the bucket while NCCL reduces it in place on the other stream.  Here:
 
-Use ``zero_grad(set_to_none=True)`` (torch's default): autograd then adopts the bucket views as
-``.grad`` without copying, and the in-place all-reduce lands directly in ``.grad``.
+* first backward after ``zero_grad(set_to_none=True)``: the layer's ``p.grad`` become views of the fresh flat bucket
+  (no kernel, same as autograd adopting them);
+* a gradient is already present and is a view of the layer's flat bucket (accumulation, or zeroed in place): the new
+  bucket is added to that flat buffer with ONE kernel on the compute stream, before the collective is ordered;
+* a gradient is present but lives elsewhere (someone assigned it): it is folded into the new bucket, which then
+  becomes the home of the layer's gradients.
+
+``no_sync()`` (as torch DDP's) skips the collective for the micro-batches inside it; the all-reduce of the last
+micro-batch then carries the accumulated sum.  Call ``finish()`` before ``optimizer.step()`` / ``zero_grad``.
+
+SM budget: the NCCL kernel keeps its CTAs (NCCL_MAX_CTAS) resident while a bucket is in flight.  The library's
+persistent kernels partition their work statically over the CTAs they launch, so a CTA that has to wait for an SM held
+by NCCL doubles that kernel's time.  From the first bucket until ``finish()`` the library is therefore told to size its
+grids for ``SMs - comm_sms`` (``gxa_set_sm_limit``); forward and the first backward layer use the whole device.
 """
 from __future__ import annotations
 
+import contextlib
 import os
-from typing import List, Optional
+from typing import Dict, List, Optional
 
 import torch
 import torch.distributed as dist
+
+from .functional import PARAM_SHAPES, bucket_layout
 
 
 class DataParallelGrads:
@@ -34,24 +49,58 @@ class DataParallelGrads:
         self.average = average
         self.comm_stream = torch.cuda.Stream() if torch.cuda.is_available() else None
         self.pending: List = []
-        self.buckets: List[torch.Tensor] = []
-        # diagnostics only (tools/, never bench.py's reported line): time the step without the collective
+        self.require_sync = True
+        self._home: Dict[int, torch.Tensor] = {}       # id(layer) -> flat bucket its p.grad are views of
+        self._touched: List[torch.Tensor] = []
         if comm_sms is None:
             comm_sms = int(os.environ.get("GXA_DP_COMM_SMS", os.environ.get("NCCL_MAX_CTAS", "16")))
         self.comm_sms = max(0, comm_sms)
         self._limited = False
+        # diagnostics only (tools/, never bench.py's reported line): time the step without the collective
         self._diag_skip = os.environ.get("GXA_DP_DIAG_NO_ALLREDUCE") == "1"
         fusion.grad_hook = self._on_layer_grads
 
-    # called from BlockFn.backward (autograd thread) right after the layer's kernels were enqueued
-    def _on_layer_grads(self, token, bucket: torch.Tensor) -> None:
-        if self.world == 1 or self._diag_skip:
-            return
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Gradient accumulation: backward passes inside accumulate locally; the next backward outside all-reduces."""
+        old, self.require_sync = self.require_sync, False
+        try:
+            yield
+        finally:
+            self.require_sync = old
+
+    def _views(self, layer, flat: torch.Tensor):
+        D = layer.d_model
+        sizes, offs, _ = bucket_layout(D)
+        return [flat[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
+
+    # called from BlockFn.backward (autograd thread) right after the layer's kernels were enqueued; returns True:
+    # "the layer's parameter gradients are installed, do not pass them to autograd"
+    def _on_layer_grads(self, layer, bucket: torch.Tensor) -> bool:
+        params = list(layer._params())
+        views = self._views(layer, bucket)
+        home = self._home.get(id(layer))
+        at_home = home is not None and home.device == bucket.device and all(
+            p.grad is not None and p.grad.data_ptr() == v.data_ptr() and p.grad.shape == v.shape
+            for p, v in zip(params, self._views(layer, home)))
+        if at_home:
+            home.add_(bucket)                                   # accumulate: one kernel over the flat buffer
+            target = home
+        else:
+            with torch.no_grad():
+                for p, v in zip(params, views):
+                    if p.grad is not None:                      # a gradient that lives elsewhere: fold it in, re-home
+                        v.add_(p.grad.to(v.dtype).view_as(v))
+                    p.grad = v
+            self._home[id(layer)] = bucket
+            target = bucket
+        if self.world == 1 or self._diag_skip or not self.require_sync:
+            return True
         if self.comm_stream is None:           # CPU/gloo (tests): synchronous
             if self.average:
-                bucket.div_(self.world)
-            dist.all_reduce(bucket, group=self.pg)
-            return
+                target.div_(self.world)
+            dist.all_reduce(target, group=self.pg)
+            return True
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream())
         if not self._limited and self.comm_sms > 0:      # kernels enqueued from here on share the device with NCCL
@@ -63,9 +112,10 @@ class DataParallelGrads:
             self.comm_stream.wait_event(ready)
             # NCCL averages inside the collective: no separate pass over the bucket on the communication stream
             op = dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM
-            self.pending.append(dist.all_reduce(bucket, op=op, group=self.pg, async_op=True))
-        bucket.record_stream(self.comm_stream)
-        self.buckets.append(bucket)
+            self.pending.append(dist.all_reduce(target, op=op, group=self.pg, async_op=True))
+        target.record_stream(self.comm_stream)
+        self._touched.append(target)
+        return True
 
     def broadcast_parameters(self, src: int = 0) -> None:
         if self.world == 1:
@@ -74,15 +124,19 @@ class DataParallelGrads:
             dist.broadcast(p.data, src, group=self.pg)
 
     def finish(self) -> None:
-        """Call after backward: reduces the stack-level grads and joins the communication stream."""
-        if self.world == 1:
+        """Call after backward (of a synchronising micro-batch): reduces the stack-level grads and joins the
+        communication stream.  After it returns, every ``p.grad`` is ordered on the current stream."""
+        if self.world == 1 or not self.require_sync:
             return
         rest = [p.grad for n, p in self.fusion.named_parameters() if not n.startswith("layers.") and p.grad is not None]
-        if rest:
+        if rest and not self._diag_skip:
             flat = torch.cat([g.reshape(-1) for g in rest])
-            if self.average:
-                flat.div_(self.world)
-            dist.all_reduce(flat, group=self.pg)
+            if self.comm_stream is None:
+                if self.average:
+                    flat.div_(self.world)
+                dist.all_reduce(flat, group=self.pg)
+            else:
+                dist.all_reduce(flat, op=dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM, group=self.pg)
             o = 0
             for g in rest:
                 g.copy_(flat[o:o + g.numel()].view_as(g))
@@ -96,7 +150,7 @@ class DataParallelGrads:
         if self.comm_stream is not None:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         self.pending.clear()
-        self.buckets.clear()
+        self._touched.clear()
 
 
 def shard_batch(global_batch: int, rank: int, world: int):

@@ -25,3 +25,11 @@ def pytest_collection_modifyitems(config, items):
     for it in items:
         if "gpu" in it.keywords:
             it.add_marker(skip)
+
+
+def pytest_sessionfinish(session, exitstatus):
+    try:
+        import gpu_util
+        gpu_util.dump_errlog()
+    except Exception:
+        pass

@@ -60,3 +60,31 @@ def gemm(A_log, B_log, a_mn=False, b_mn=False, epi=_lib.EPI_F32, bias=None, aux=
 
 def np_dev(a, dtype=torch.float32):
     return torch.from_numpy(np.ascontiguousarray(a)).to("cuda", dtype)
+
+
+# ---- measured parity errors, written next to the test log so that a tolerance is a measurement, not an argument
+_ERRLOG = {}
+
+
+def record_err(case: str, name: str, value: float) -> None:
+    _ERRLOG.setdefault(case, {})[name] = float(value)
+
+
+def dump_errlog() -> None:
+    import json
+    import os
+    if not _ERRLOG:
+        return
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        path = os.path.join(out, "parity_errors.json")
+        old = {}
+        if os.path.exists(path):
+            with open(path) as f:
+                old = json.load(f)
+        old.update(_ERRLOG)
+        with open(path, "w") as f:
+            json.dump(old, f, indent=1, sort_keys=True)
+    except OSError:
+        pass

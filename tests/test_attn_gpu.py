@@ -70,6 +70,10 @@ def run(B, H, Lq, Lk, lengths, seed=0, garbage=True):
     (3, 2, 100, 200, [200, 77, 1]),
     (4, 4, 448, 750, [750, 60, 333, 64]),
     (2, 2, 50, 130, [130, 0]),
+    # BASELINE widths (configs 2, 3, 4): every head index up to 11 / 15 / 19, six key blocks, ragged and empty samples
+    (2, 12, 448, 750, [750, 60]),
+    (3, 16, 448, 750, [750, 333, 0]),
+    (2, 20, 448, 750, [61, 750]),
 ])
 def test_attention_fwd_bwd(B, H, Lq, Lk, lengths):
     r = run(B, H, Lq, Lk, lengths)
@@ -144,6 +148,7 @@ def run_dropout(B, H, Lq, Lk, lengths, p, seed64, seed=0):
     (2, 6, 448, 250, None, 0.1),
     (3, 2, 100, 201, [201, 77, 30], 0.25),         # odd Lk: pair counters restart per row
     (2, 4, 448, 750, [750, 333], 0.1),
+    (2, 16, 448, 750, [750, 60], 0.1),             # config 3's heads and lengths
 ])
 def test_attention_dropout_matches_reference_with_same_mask(B, H, Lq, Lk, lengths, p):
     r = run_dropout(B, H, Lq, Lk, lengths, p, seed64=0x1234ABCD5678EF01)

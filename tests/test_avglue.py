@@ -17,7 +17,7 @@ def _load():
 
 def _rel(a, b):
     a, b = a.double().cpu(), torch.as_tensor(b).double()
-    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))      # max-norm, as everywhere else
 
 
 def test_positional_table_matches_reference_buffer():
@@ -40,7 +40,7 @@ def test_cpu_input_fails_loudly():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision,tol_y,tol_g", [("fp32", 1e-4, 1e-4), ("bf16", 2e-2, 3e-2)])
+@pytest.mark.parametrize("precision,tol_y,tol_g", [("fp32", 1e-4, 1e-4), ("bf16", 2e-2, 2e-2)])
 def test_glue_matches_reference(precision, tol_y, tol_g):
     g = _load()
     B, T, FA, FV, D = (int(v) for v in g["spec"])

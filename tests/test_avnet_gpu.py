@@ -58,7 +58,7 @@ def test_avnet_call_replayed(prec, tol):
         G.set_default_precision(None)
     assert fused.dtype == torch.float32 and tuple(fused.shape) == (B, L, D)
     assert rel_err(fused.detach().cpu(), torch.from_numpy(g["fused"])) < tol
-    gtol = tol if prec == "fp32" else 3e-2
+    gtol = tol
     assert rel_err(a.grad.cpu(), torch.from_numpy(g["d_audio"])) < gtol
     assert rel_err(v.grad.cpu(), torch.from_numpy(g["d_video"])) < gtol
     for n, p in mod.named_parameters():

@@ -68,3 +68,35 @@ def test_decode_cuda_graph_replay_matches_eager():
     finally:
         G.set_default_precision(None)
     assert G.launch_count() > n0
+
+
+def test_decode_at_config5_shape_matches_cpu_reference():
+    """BASELINE config 5: Whisper-small (d=768, 12 heads, 12 layers), batch 32 x beam 5, 750 cached visual frames.
+    The reference has no decode loop; its stack called on the step's query rows with the full visual memory
+    is the oracle (oracle/torch_port.py, fp32 on the host CPU)."""
+    from oracle import torch_port as TP
+    B, beams, Lk, D, H, nl = 32, 5, 750, 768, 12, 12
+    rng = __import__("numpy").random.RandomState(5)
+    lengths = [int(v) for v in rng.randint(60, Lk + 1, size=B)]
+    lengths[0], lengths[1] = Lk, 1
+    p, x, xa, mask, mod = _setup(B, beams, Lk, D, H, nl, lengths, seed=55)
+    with torch.no_grad():
+        yr = TP.fusion_forward(TP.to_torch(p), torch.from_numpy(x), torch.from_numpy(xa), torch.from_numpy(mask), H, nl)
+    xt, xat, mt = np_dev(x), np_dev(xa), torch.from_numpy(mask).cuda()
+    G.set_default_precision("bf16")
+    try:
+        with torch.no_grad():
+            y_full = mod(xt, xat, video_mask=mt)
+            st = G.DecodeState(mod, xat, mt)
+            assert st.kv_cache_bytes() == nl * B * Lk * 2 * D * 2
+            y_eager = st.step(xt).clone()
+            st.capture(xt.shape)
+            y_graph = st.step(xt).clone()
+        torch.cuda.synchronize()
+    finally:
+        G.set_default_precision(None)
+    assert torch.isfinite(y_eager).all()
+    assert rel_err(y_full.cpu(), yr) < 2e-2
+    assert rel_err(y_eager.cpu(), yr) < 2e-2
+    assert rel_err(y_graph.cpu(), yr) < 2e-2
+    assert rel_err(y_graph, y_eager) < 1e-5

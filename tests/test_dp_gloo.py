@@ -86,9 +86,9 @@ def _worker(rank: int, world: int, port: int, average: bool):
             views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
             for v, key in zip(views, LAYER_KEYS):
                 v.copy_(local[f"layers.{i}.{key}"])
-            model.grad_hook(model.layers[i], bucket)
+            assert model.grad_hook(model.layers[i], bucket) is True      # the hook installs p.grad itself
             for v, prm in zip(views, model.layers[i]._params()):
-                prm.grad = v
+                assert prm.grad is not None and prm.grad.data_ptr() == v.data_ptr()
         for n, prm in model.named_parameters():
             if not n.startswith("layers."):
                 prm.grad = local[n].clone()
@@ -101,6 +101,43 @@ def _worker(rank: int, world: int, port: int, average: bool):
             den = float(ref.abs().max())
             err = float((prm.grad - ref).abs().max()) / (den if den > 0 else 1.0)
             assert err < 2e-5, (n, err)
+
+        # ---- gradient accumulation (reference: accumulate_grad_batches, config.py:42): two micro-batches, the first one
+        # inside no_sync(); p.grad is already present in the second backward, so the new bucket has to be ADDED to the
+        # flat buffer behind p.grad before the single all-reduce.  Layer 0 starts from a "foreign" gradient (assigned by
+        # someone else, not a view of a bucket) to cover the re-homing path.
+        model.zero_grad(set_to_none=True)
+        foreign = {}
+        for prm, key in zip(model.layers[0]._params(), LAYER_KEYS):
+            foreign[key] = torch.full_like(prm, 0.25)
+            prm.grad = foreign[key].clone()
+        half = (b1 - b0 + 1) // 2
+        micro = [(b0, b0 + half), (b0 + half, b1)]
+        for step, (m0, m1) in enumerate(micro):
+            if m1 <= m0:
+                loc = {k: torch.zeros_like(v) for k, v in state.items()}
+            else:
+                loc = _port_grads(state, audio[m0:m1], video[m0:m1], mask[m0:m1], dy[m0:m1])
+            ctxm = ddp.no_sync() if step == 0 else __import__("contextlib").nullcontext()
+            with ctxm:
+                for i in reversed(range(LAYERS)):
+                    bucket = torch.zeros(total)
+                    views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
+                    for v, key in zip(views, LAYER_KEYS):
+                        v.copy_(loc[f"layers.{i}.{key}"])
+                    model.grad_hook(model.layers[i], bucket)
+                for n, prm in model.named_parameters():
+                    if not n.startswith("layers."):
+                        prm.grad = loc[n].clone() if prm.grad is None else prm.grad + loc[n]
+                ddp.finish()                                    # a no-op inside no_sync()
+        for n, prm in model.named_parameters():
+            ref = full[n] * scale
+            if n.startswith("layers.0."):
+                # every rank folded the same foreign 0.25 in BEFORE the collective: AVG keeps it, SUM multiplies it
+                ref = ref + 0.25 * (1.0 if average else world)
+            den = float(ref.abs().max())
+            err = float((prm.grad - ref).abs().max()) / (den if den > 0 else 1.0)
+            assert err < 2e-5, ("accumulate", n, err)
 
         # sharding helpers: every rank derives the same partition from the same lengths
         lengths = [750, 60, 400, 399, 90, 700, 61, 333]
