@@ -4,20 +4,30 @@ configs[2]: d=1024, 16 heads, 24 gated x-attn layers, global batch 64, Lq=448 x 
 over N GPUs (strong scaling: the global batch is fixed).
 
     python bench.py [--gpus N --steps K --warmup W]          # product arm (CUDA, libgxa_b200.so)
-    python bench.py --impl reference ...                      # reference's CPU path (oracle port) on host cores
+    python bench.py --impl reference ...                      # the reference's own CPU path on the host cores
+    python bench.py --workload whisper-large-c4 [--shards balanced]     # config 4: variable-length visual memories
+    python bench.py --workload whisper-small-c2                          # config 2
 
-A step = H2D of the step's inputs (e2e only) -> GatedCrossModalFusion forward (24 layers) -> loss ->
+A step = H2D of the step's inputs (e2e only) -> GatedCrossModalFusion forward (all layers) -> loss ->
 backward (all dgrad + wgrad) -> per-layer gradient all-reduce (N>1) -> D2H of the loss (e2e only).
 The fp32->bf16 weight cast is redone every step (a real optimizer step would change the weights).
 Prints ONE JSON line on rank 0.
+
+Besides the contract keys the line carries
+  roofline      the dominant kernel (FFN1 GEMM + bias + erf-GELU) timed alone, vs the measured burst bf16 peak
+  step_roofline the whole step's algorithmic FLOPs vs the measured sustained bf16 peak
+  cpu_baseline  the reference module (oracle/_ref, a git-ignored copy made by build(); else the oracle port) on the host
+  gpu_baseline  the reference's op sequence in stock PyTorch (eager, autocast bf16) on the SAME GPU, same config
+  dp_grad_check (N>1) all-reduced gradients of the N shards vs a full-batch run on every rank, dropout off
 """
 from __future__ import annotations
 
 import argparse
+import contextlib
 import json
 import os
 
-os.environ.setdefault("NCCL_MAX_CTAS", "16")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
+os.environ.setdefault("NCCL_MAX_CTAS", "8")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
 import statistics
 import subprocess
 import sys
@@ -30,17 +40,25 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: (D, H, layers, global batch, Lq, Lk)
-    "whisper-medium-c3": (1024, 16, 24, 64, 448, 750),
-    "whisper-small-c2": (768, 12, 12, 16, 448, 750),
-    "whisper-tiny-c1": (384, 6, 1, 2, 448, 250),
+    # name: (D, H, layers, global batch, Lq, Lk, variable key lengths)
+    "whisper-medium-c3": (1024, 16, 24, 64, 448, 750, False),
+    "whisper-small-c2": (768, 12, 12, 16, 448, 750, False),
+    "whisper-large-c4": (1280, 20, 32, 64, 448, 750, True),      # len_b ~ U[60, 750], seed 1234
+    "whisper-tiny-c1": (384, 6, 1, 2, 448, 250, False),
 }
 METRIC = "gated-xattn fwd+bwd tokens/s at Whisper-medium"
 
 
-def block_fwd_flops(B, Lq, Lk, D):
-    """20 B Lq D^2 + 4 (sum len) D^2 + 4 Lq (sum len) D, full-length keys."""
-    return 20 * B * Lq * D * D + 4 * B * Lk * D * D + 4 * B * Lq * Lk * D
+def block_fwd_flops(B, Lq, sum_len, D):
+    """20 B Lq D^2 + 4 (sum len) D^2 + 4 Lq (sum len) D -- unpadded key counts."""
+    return 20 * B * Lq * D * D + 4 * sum_len * D * D + 4 * Lq * sum_len * D
+
+
+def global_lengths(GB, Lk, variable):
+    if not variable:
+        return [Lk] * GB
+    import numpy as np
+    return [int(v) for v in np.random.RandomState(1234).randint(60, Lk + 1, size=GB)]
 
 
 def peaks():
@@ -51,6 +69,18 @@ def peaks():
                     hbm=float(p["hbm_gbs"]), source="measured")
     except Exception:
         return dict(burst=1590.0, sustained=1400.0, hbm=6650.0, source="fallback")
+
+
+def measured_traffic(M, N, K):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel per launch, from the committed ncu captures
+    (profiles/roofline_traffic.json); None for shapes that were never captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            t = json.load(f)
+        e = t.get(f"{M}x{N}x{K}")
+        return (float(e["dram_bytes"]), e.get("source")) if e else (None, None)
+    except Exception:
+        return None, None
 
 
 class ClockSampler:
@@ -92,72 +122,170 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads, sample_B=2, sample_layers=2, reps=3, dropout=0.1):
-    """The reference's CPU path (oracle/torch_port.py: same ATen CPU kernels as the reference module) on a bounded
-    sample: `sample_layers` layers of the stack at batch `sample_B`, fwd+bwd, extrapolated linearly to `layers`."""
-    from oracle import gxa_oracle as O
-    from oracle import torch_port as TP
+# ------------------------------------------------------------------------------------------------ reference arms
+def load_reference_module():
+    """The UNMODIFIED reference file (models/gate_cross_attention.py), copied by __graft_entry__.build() into the
+    git-ignored oracle/_ref/ so that it travels to the GPU box.  Returns (module, "reference") or (None, "port")."""
+    path = os.path.join(ROOT, "oracle", "_ref", "gate_cross_attention.py")
+    if not os.path.exists(path):
+        return None, "port"
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gxa_reference_gate_cross_attention", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod, "reference"
+
+
+def init_like_bench(model):
+    """non-trivial biases / LN affine, nonzero gates (the default 0 gates make the block the identity)."""
+    with torch.no_grad():
+        for n, p in model.named_parameters():
+            if n.endswith("attn_gate"):
+                p.fill_(0.7)
+            elif n.endswith("ff_gate"):
+                p.fill_(-0.4)
+            elif "ln" in n and n.endswith("weight"):
+                p.copy_(1 + 0.1 * torch.randn_like(p))
+            elif n.endswith("bias"):
+                p.uniform_(-0.1, 0.1)
+
+
+class _StockBlock(torch.nn.Module):
+    """The reference block's statements (models/gate_cross_attention.py:13-50) from stock torch modules; used for the
+    baselines only when oracle/_ref is absent (kind "port")."""
+
+    def __init__(self, d, h, p):
+        super().__init__()
+        nn = torch.nn
+        self.attn = nn.MultiheadAttention(d, h, dropout=p, batch_first=True)
+        self.attn_ln, self.ff_ln = nn.LayerNorm(d), nn.LayerNorm(d)
+        self.attn_gate = nn.Parameter(torch.tensor([0.]))
+        self.ff_gate = nn.Parameter(torch.tensor([0.]))
+        self.ff = nn.Sequential(nn.Linear(d, 4 * d), nn.GELU(), nn.Linear(4 * d, d), nn.Dropout(p))
+
+    def forward(self, x, xa, mask):
+        h = self.attn_ln(x.float()).type(x.dtype)
+        x = x + self.attn(h, xa, xa, key_padding_mask=mask, need_weights=False)[0] * self.attn_gate.tanh()
+        return x + self.ff(self.ff_ln(x.float()).type(x.dtype)) * self.ff_gate.tanh()
+
+
+class _StockFusion(torch.nn.Module):
+    def __init__(self, d, h, n, p):
+        super().__init__()
+        nn = torch.nn
+        self.audio_proj, self.video_proj = nn.Linear(d, d), nn.Linear(d, d)
+        self.layers = nn.ModuleList([_StockBlock(d, h, p) for _ in range(n)])
+        self.ln_post = nn.LayerNorm(d)
+
+    def forward(self, a, v, audio_mask=None, video_mask=None):
+        x, xa = self.audio_proj(a), self.video_proj(v)
+        for layer in self.layers:
+            x = layer(x, xa, video_mask)
+        return self.ln_post(x.float()).type(x.dtype)
+
+
+def make_reference_stack(D, H, layers, dropout):
+    ref, kind = load_reference_module()
+    torch.manual_seed(1234)
+    model = ref.GatedCrossModalFusion(D, H, layers, dropout=dropout) if ref is not None else _StockFusion(D, H, layers, dropout)
+    init_like_bench(model)
+    return model.train(), kind
+
+
+def cpu_reference_step_fn(D, H, layers, Lq, Lk, lengths, threads, sample_B, dropout):
+    """One fwd+bwd of the reference stack (all `layers` layers, training mode, fp32 -- the reference's CPU path) on a
+    bounded sample of `sample_B` samples of the workload."""
     torch.set_num_threads(threads)
-    p = TP.to_torch(O.make_params(O.fusion_param_shapes(D, sample_layers), 1234), requires_grad=True)
-    x, xa, mask, dy = O.make_inputs(sample_B, Lq, Lk, D, 1234)
-    xt, xat = torch.from_numpy(x).requires_grad_(True), torch.from_numpy(xa).requires_grad_(True)
-    mt, dyt = torch.from_numpy(mask), torch.from_numpy(dy)
-    times = []
-    for i in range(reps + 1):
-        t0 = time.perf_counter()
-        y = TP.fusion_forward(p, xt, xat, mt, H, sample_layers, dropout, True)
-        y.backward(dyt)
-        times.append(time.perf_counter() - t0)
-    t = statistics.median(times[1:])
-    t_full = t * layers / sample_layers
-    return sample_B * Lq / t_full, t, f"{sample_layers} of {layers} layers at batch {sample_B} (Lq={Lq}, Lk={Lk}, D={D}), fp32 fwd+bwd, " \
-                                      f"median of {reps} after 1 warm-up, extrapolated linearly in layers"
+    model, kind = make_reference_stack(D, H, layers, dropout)
+    g = torch.Generator().manual_seed(1234)
+    a = torch.randn(sample_B, Lq, D, generator=g).requires_grad_(True)
+    v = torch.randn(sample_B, Lk, D, generator=g).requires_grad_(True)
+    ln = torch.tensor(lengths[:sample_B])
+    mask = torch.arange(Lk)[None, :] >= ln[:, None]
+    dy = torch.randn(sample_B, Lq, D, generator=g)
+
+    def step():
+        model.zero_grad(set_to_none=True)
+        a.grad = v.grad = None
+        model(a, v, video_mask=mask).backward(dy)
+    what = ("unmodified reference module (oracle/_ref/gate_cross_attention.py)" if kind == "reference"
+            else "stock-torch restatement of the reference block (oracle/_ref absent)")
+    sample = (f"{sample_B} of the workload's samples per step through ALL {layers} layers (Lq={Lq}, Lk={Lk}, D={D}, "
+              f"dropout {dropout}, train mode), fp32 fwd+bwd on {threads} host threads, {what}; no extrapolation in depth")
+    return step, kind, sample
 
 
-def run_reference(args, D, H, layers, GB, Lq, Lk):
-    """--impl reference: the reference's own CPU implementation of the path on the host cores.  The reference is a
-    Python module that cannot travel to the GPU box, so this is the oracle port (same ATen CPU kernels)."""
+def run_reference(args, D, H, layers, GB, Lq, Lk, variable):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores, rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample_B, sample_layers = 2, 2
-    from oracle import gxa_oracle as O
-    from oracle import torch_port as TP
-    torch.set_num_threads(threads)
-    p = TP.to_torch(O.make_params(O.fusion_param_shapes(D, sample_layers), 1234), requires_grad=True)
-    x, xa, mask, dy = O.make_inputs(sample_B, Lq, Lk, D, 1234)
-    xt, xat = torch.from_numpy(x).requires_grad_(True), torch.from_numpy(xa).requires_grad_(True)
-    mt, dyt = torch.from_numpy(mask), torch.from_numpy(dy)
-
-    def step():
-        TP.fusion_forward(p, xt, xat, mt, H, sample_layers, args.dropout, True).backward(dyt)
-
+    sample_B = args.ref_batch
+    step, kind, sample = cpu_reference_step_fn(D, H, layers, Lq, Lk, global_lengths(GB, Lk, variable), threads, sample_B,
+                                               args.dropout)
     for _ in range(args.warmup):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     t = (time.perf_counter() - t0) / args.steps
-    t_full = t * layers / sample_layers           # seconds for sample_B samples through all layers
-    value = sample_B * Lq / t_full
-    sample = (f"{sample_layers} of {layers} layers at batch {sample_B} per step, fp32 fwd+bwd on {threads} host threads, "
-              "extrapolated linearly in layers; reference module is Python and cannot travel -> oracle/torch_port.py "
-              "(same ATen CPU kernels)")
+    value = sample_B * Lq / t
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "d_model": D, "heads": H, "layers": layers, "global_batch": GB,
-                   "Lq": Lq, "Lk": Lk, "dropout": args.dropout, "mode": "train"},
-        "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": "port", "sample": sample},
+                   "Lq": Lq, "Lk": Lk, "dropout": args.dropout, "mode": "train", "sample_batch": sample_B},
+        "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
+def gpu_baseline(D, H, layers, B, Lq, Lk, lengths, dropout, steps=3, warmup=2):
+    """the 'existing Blackwell path' -- the reference module itself (oracle/_ref; else its statements in
+    stock torch modules), eager, torch.autocast(bf16), fp32 parameters, on this GPU at this rank's shard of the workload.
+    Timed with CUDA events outside the product's timed regions."""
+    model, kind = make_reference_stack(D, H, layers, dropout)
+    model.cuda()
+    torch.cuda.reset_peak_memory_stats()
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    a = torch.randn(B, Lq, D, device="cuda", generator=g).requires_grad_(True)
+    v = torch.randn(B, Lk, D, device="cuda", generator=g).requires_grad_(True)
+    mask = torch.arange(Lk, device="cuda")[None, :] >= torch.tensor(lengths, device="cuda")[:, None]
+    dy = torch.randn(B, Lq, D, device="cuda", generator=g)
+
+    def step():
+        model.zero_grad(set_to_none=True)
+        a.grad = v.grad = None
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = model(a, v, video_mask=mask)
+        y.backward(dy)
+    try:
+        for _ in range(warmup):
+            step()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out = {"impl": "torch eager + autocast(bf16), " + ("unmodified reference module (oracle/_ref)" if kind == "reference"
+                                                           else "stock-torch restatement of the reference block"),
+               "value": B * Lq / (ms * 1e-3), "unit": "tokens/s (this GPU's shard)", "ms_per_step": ms, "per_gpu_batch": B,
+               "steps": steps, "warmup": warmup, "peak_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30,
+               "torch": torch.__version__}
+    except torch.OutOfMemoryError as e:      # report, do not extrapolate
+        out = {"unavailable": "out of memory: " + str(e)[:120]}
+    del model, a, v, dy
+    torch.cuda.empty_cache()
+    return out
+
+
 def time_dominant_kernel(M, D, pk):
     """FFN1 GEMM with the fused bias + erf-GELU epilogue at this rank's shape, CUDA events on the launch stream."""
-    import ctypes as C  # noqa: F401
     from mocov2_whisper_flamingo_b200 import _lib
     L = _lib.lib()
     N, K = 4 * D, D
@@ -183,19 +311,19 @@ def time_dominant_kernel(M, D, pk):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / n
     tf = 2.0 * M * N * K / (ms * 1e-3) / 1e12
+    traffic, src = measured_traffic(M, N, K)
     return {"bound": "tensor", "kernel": "gemm_tc2_kernel<EPI_BIAS_GELU> (CTA-pair 256x256 tiles; FFN1 + bias + erf-GELU and its derivative, M=%d N=%d K=%d)" % (M, N, K),
             "achieved": tf, "peak": pk["burst"], "unit": "TFLOP/s", "frac": tf / pk["burst"],
             "peak_source": pk["source"] + " bf16_tflops (burst: kernel timed alone)", "ms_per_launch": ms,
-            # dram__bytes_read.sum + dram__bytes_write.sum of this kernel at this shape, one ncu --set full capture
-            # (profiles/r01_c_ncu_gemm_pair.txt: 67.7 MB read + 417.6 MB written); other shapes were not captured
-            "traffic": 485.3e6 if (M, N, K) == (28672, 4096, 1024) else None,
+            "traffic": traffic, "traffic_source": src,
             "algorithmic_bytes": 2.0 * (M * K + N * K + 2 * M * N)}
 
 
-def run_product(args, D, H, layers, GB, Lq, Lk):
+# ------------------------------------------------------------------------------------------------ product arm
+def run_product(args, D, H, layers, GB, Lq, Lk, variable):
     import torch.distributed as dist
     import mocov2_whisper_flamingo_b200 as G
-    from mocov2_whisper_flamingo_b200.parallel import DataParallelGrads, shard_batch
+    from mocov2_whisper_flamingo_b200.parallel import DataParallelGrads, balanced_shards, shard_batch
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -204,20 +332,18 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    b0, b1 = shard_batch(GB, rank, world)
-    B = b1 - b0
+    lengths_g = global_lengths(GB, Lk, variable)
+    if args.shards == "balanced":
+        mine = balanced_shards(lengths_g, world)[rank]       # length-sorted serpentine
+    else:
+        b0, b1 = shard_batch(GB, rank, world)
+        mine = list(range(b0, b1))
+    B = len(mine)
+    lengths = [lengths_g[i] for i in mine]
+    sum_len = sum(lengths)
     torch.manual_seed(1234)
     model = G.GatedCrossModalFusion(D, H, layers, dropout=args.dropout)   # reference default: config.py:21 fusion_dropout 0.1
-    with torch.no_grad():                      # non-trivial biases / LN affine, nonzero gates
-        for n, p in model.named_parameters():
-            if n.endswith("attn_gate"):
-                p.fill_(0.7)
-            elif n.endswith("ff_gate"):
-                p.fill_(-0.4)
-            elif "ln" in n and n.endswith("weight"):
-                p.copy_(1 + 0.1 * torch.randn_like(p))
-            elif n.endswith("bias"):
-                p.uniform_(-0.1, 0.1)
+    init_like_bench(model)
     model.cuda().train()
     G.set_default_precision("bf16")
     ddp = DataParallelGrads(model) if world > 1 else None
@@ -232,8 +358,11 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
         del probe
     g = torch.Generator().manual_seed(1234 + rank)
     audio_h = torch.randn(B, Lq, D, generator=g).pin_memory()
-    video_h = torch.randn(B, Lk, D, generator=g).pin_memory()
-    mask_h = torch.zeros(B, Lk, dtype=torch.bool).pin_memory()       # len_b = Lk, mask still passed (8d2)
+    video_h = torch.randn(B, Lk, D, generator=g)
+    mask_h = (torch.arange(Lk)[None, :] >= torch.tensor(lengths)[:, None])       # True = padded key; passed even when all False (8d2)
+    if variable:
+        video_h = torch.where(mask_h[:, :, None], 1e3 * video_h, video_h)       # padded rows hold garbage: masking must hide it
+    video_h, mask_h = video_h.pin_memory(), mask_h.pin_memory()
     loss_h = torch.zeros(1).pin_memory()
     audio_d, video_d, mask_d = audio_h.cuda(), video_h.cuda(), mask_h.cuda()
     dy = torch.randn(B, Lq, D, device="cuda")
@@ -299,20 +428,27 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
         if world > 1:
             dist.barrier()
         clocks = sampler.stop() if sampler else None
-        ms = torch.tensor([e0.elapsed_time(e1) / steps], device="cuda")
+        ms_own = e0.elapsed_time(e1) / steps
+        ms = torch.tensor([ms_own], device="cuda")
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms[0]), clocks
+        return float(ms[0]), clocks, ms_own
 
     for _ in range(max(args.warmup, 3)):
         step(False)
     l0 = G.launch_count()
-    ms, clocks = timed(False, args.steps, ClockSampler(local) if rank == 0 else None)
+    ms, clocks, ms_own = timed(False, args.steps, ClockSampler(local) if rank == 0 else None)
     launches = G.launch_count() - l0
     step(True)
-    ms_e2e, clocks_e2e = timed(True, args.steps, ClockSampler(local) if rank == 0 else None)
+    ms_e2e, clocks_e2e, _ = timed(True, args.steps, ClockSampler(local) if rank == 0 else None)
+    # per-rank step times: with variable-length memories the slowest rank sets the step
+    rank_ms = [ms_own]
+    if world > 1:
+        t = torch.tensor([ms_own], device="cuda")
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        rank_ms = [float(x[0]) for x in allt]
     # diagnostic, outside every timed region: what the box's host->device link gives for this step's pinned inputs alone
-    # (e2e hides the copy behind the previous step only if 314 MB move in less than a step)
     h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     h0.record()
@@ -321,9 +457,55 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
     h1.record()
     torch.cuda.synchronize()
     h2d_gbs = (audio_h.numel() + video_h.numel()) * 4 / (h0.elapsed_time(h1) * 1e-3) / 1e9
+
+    # ---- data-parallel correctness on the hardware (N > 1): dropout off, one step on the shards with the per-layer
+    # all-reduce vs ONE full-batch step on every rank.  AVG over ranks of the shard gradients = full-batch gradient / N.
+    dp_check = None
+    if ddp:
+        model.eval()
+        gg = torch.Generator(device="cuda").manual_seed(4321)
+        a_g = torch.randn(GB, Lq, D, device="cuda", generator=gg)
+        v_g = torch.randn(GB, Lk, D, device="cuda", generator=gg)
+        dy_g = torch.randn(GB, Lq, D, device="cuda", generator=gg)
+        m_g = (torch.arange(Lk, device="cuda")[None, :] >= torch.tensor(lengths_g, device="cuda")[:, None])
+        idx = torch.tensor(mine, device="cuda")
+        hook, model.grad_hook = model.grad_hook, None           # plain full-batch run first, no collective
+        model.zero_grad(set_to_none=True)
+        (model(a_g, v_g, video_mask=m_g) * dy_g).sum().backward()
+        torch.cuda.synchronize()
+        full = {n: (p.grad / world).clone() for n, p in model.named_parameters()}
+        model.grad_hook = hook
+        worst = 0.0
+        for accumulate in (False, True):
+            model.zero_grad(set_to_none=True)
+            parts = [idx] if not accumulate else [idx[: (B + 1) // 2], idx[(B + 1) // 2:]]
+            for j, part in enumerate(parts):
+                last = j == len(parts) - 1
+                if part.numel() == 0 and not last:
+                    continue
+                with (contextlib.nullcontext() if last else ddp.no_sync()):
+                    (model(a_g[part], v_g[part], video_mask=m_g[part]) * dy_g[part]).sum().backward()
+                    ddp.finish()
+            torch.cuda.synchronize()
+            for n, p in model.named_parameters():
+                ref, got = full[n], p.grad
+                den = float(ref.abs().max())
+                if n.endswith("in_proj_bias"):                      # the bk third is rounding noise around 0
+                    ref, got = torch.cat([ref[:D], ref[2 * D:]]), torch.cat([got[:D], got[2 * D:]])
+                if den > 0:
+                    worst = max(worst, float((got - ref).abs().max()) / den)
+        wt = torch.tensor([worst], device="cuda")
+        dist.all_reduce(wt, op=dist.ReduceOp.MAX)
+        dp_check = {"max_rel_err": float(wt[0]), "tolerance": 5e-3, "ok": bool(float(wt[0]) < 5e-3),
+                    "what": "AVG-all-reduced shard gradients (plain step, and 2 micro-batches with no_sync) vs full-batch gradient / N "
+                            "on every rank, all parameters, dropout off, bf16 mode (differences: fp32 summation order and the bf16 "
+                            "roundings it flips)"}
+        model.zero_grad(set_to_none=True)
+        del a_g, v_g, dy_g, full
+        model.train()
     pk = peaks()
     tokens = GB * Lq
-    flops_gpu = 3 * layers * block_fwd_flops(B, Lq, Lk, D)
+    flops_gpu = 3 * layers * block_fwd_flops(B, Lq, sum_len, D)
     roof = time_dominant_kernel(B * Lq, D, pk)
     out = None
     if rank == 0:
@@ -334,6 +516,8 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": args.workload, "d_model": D, "heads": H, "layers": layers, "global_batch": GB,
                        "per_gpu_batch": B, "Lq": Lq, "Lk": Lk, "parallelism": f"dp{world}", "dropout": args.dropout, "mode": "train",
+                       "key_lengths": "U[60,750] seed 1234, 1e3-scale garbage in padded rows" if variable else "full (mask passed, all False)",
+                       "shards": args.shards, "sum_len_rank0": sum_len,
                        "step": "fwd + bwd (dgrad+wgrad) + weight bf16 re-cast" + (" + per-layer NCCL grad all-reduce" if world > 1 else ""),
                        "l2": "per-step working set (>30 GB of activations) far exceeds the 126 MB L2; no flush needed"},
             "clocks": clocks, "gpu_launches": launches,
@@ -342,18 +526,39 @@ def run_product(args, D, H, layers, GB, Lq, Lk):
                     "d2h_bytes_per_step": 4, "h2d_link_gbs_measured": h2d_gbs, "clocks": clocks_e2e},
             "roofline": roof,
             "step_roofline": {"bound": "tensor", "achieved": step_tf, "peak": pk["sustained"], "unit": "TFLOP/s",
-                              "frac": step_tf / pk["sustained"], "frac_of_2250_spec": step_tf / 2250.0,
-                              "flops_per_step_per_gpu": flops_gpu,
+                              "frac": step_tf / pk["sustained"], "frac_of_burst": step_tf / pk["burst"],
+                              "frac_of_2250_spec": step_tf / 2250.0, "flops_per_step_per_gpu": flops_gpu,
                               "peak_source": pk["source"] + " bf16_tflops_sustained (kernels timed inside a long step)"},
         }
+        if world > 1:
+            out["rank_ms"] = rank_ms
+            out["rank_imbalance_max_over_mean"] = max(rank_ms) / (sum(rank_ms) / len(rank_ms))
+            out["dp_grad_check"] = dp_check
+    # free the product's model before the baselines (the eager baseline needs ~33 GB at config 3)
+    del model, ddp
+    torch.cuda.empty_cache()
+    gb = None
+    if not args.no_gpu_baseline:
+        gb = gpu_baseline(D, H, layers, B, Lq, Lk, lengths, args.dropout)
     if world > 1:
         dist.barrier()
     if rank == 0:
+        if gb is not None:
+            if "ms_per_step" in gb:
+                gb["speedup_of_this_library"] = gb["ms_per_step"] / ms_own
+            out["gpu_baseline"] = gb
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            v, t, sample = cpu_port_tokens_per_s(D, H, layers, Lq, Lk, threads, dropout=args.dropout)
-            out["cpu_baseline"] = {"value": v, "unit": "tokens/s", "cores": threads, "kind": "port", "sample": sample,
-                                   "seconds_per_sample": t}
+            fn, kind, sample = cpu_reference_step_fn(D, H, layers, Lq, Lk, lengths_g, threads, args.ref_batch, args.dropout)
+            fn()
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                fn()
+                ts.append(time.perf_counter() - t0)
+            t = statistics.median(ts)
+            out["cpu_baseline"] = {"value": args.ref_batch * Lq / t, "unit": "tokens/s", "cores": threads, "kind": kind,
+                                   "sample": sample + "; median of 3 after 1 warm-up", "seconds_per_step": t}
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -366,14 +571,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gxa", choices=["gxa", "reference"])
     ap.add_argument("--workload", default="whisper-medium-c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--shards", default="contiguous", choices=["contiguous", "balanced"],
+                    help="sample-to-rank assignment (balanced: parallel.balanced_shards, for variable-length memories)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true")
+    ap.add_argument("--ref-batch", type=int, default=2, help="samples per step of the CPU reference arm (bounded sample)")
     ap.add_argument("--dropout", type=float, default=0.1, help="training-mode dropout of the stack (reference config.py: 0.1)")
     args = ap.parse_args()
-    D, H, layers, GB, Lq, Lk = WORKLOADS[args.workload]
+    D, H, layers, GB, Lq, Lk, variable = WORKLOADS[args.workload]
     if args.impl == "reference":
-        run_reference(args, D, H, layers, GB, Lq, Lk)
+        run_reference(args, D, H, layers, GB, Lq, Lk, variable)
     else:
-        run_product(args, D, H, layers, GB, Lq, Lk)
+        run_product(args, D, H, layers, GB, Lq, Lk, variable)
 
 
 if __name__ == "__main__":

@@ -16,7 +16,7 @@ import bench  # noqa: E402
 import mocov2_whisper_flamingo_b200 as G  # noqa: E402
 
 wl = sys.argv[1] if len(sys.argv) > 1 else "whisper-medium-c3"
-D, H, layers, GB, Lq, Lk = bench.WORKLOADS[wl]
+D, H, layers, GB, Lq, Lk, _variable = bench.WORKLOADS[wl]
 B = int(sys.argv[2]) if len(sys.argv) > 2 else GB
 layers = int(os.environ.get("LAYERS", layers))
 torch.manual_seed(1234)
