@@ -94,7 +94,7 @@ def lib() -> C.CDLL:
 
 def check(code: int, what: str) -> None:
     if code != 0:
-        detail = lib().gxa_last_cuda_error().decode() if code == -4 else ""
+        detail = lib().gxa_last_cuda_error().decode() if code in (-3, -4) else ""
         raise RuntimeError(f"{what} failed: {_ERR.get(code, code)} {detail}".rstrip())
 
 

@@ -4,6 +4,9 @@
 #include <cstdlib>
 #include <atomic>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "gxa_gemm.cuh"
 #include "gxa_host.h"
@@ -11,10 +14,25 @@
 namespace gxa {
 
 static std::atomic<long long> g_launches{0};
-static int g_sms = 0;
+static std::atomic<int> g_sms_dev[16];     // SM count per device ordinal (0 = not queried yet)
 static char g_err[256] = "";
+static std::mutex g_init_mu;               // guards the lazily created per-device state below
+
+int set_max_smem_once_impl(const void* kernel, int bytes) {
+  static std::map<std::pair<const void*, int>, int> done;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return GXA_ERR_CUDA;
+  std::lock_guard<std::mutex> lk(g_init_mu);
+  auto key = std::make_pair(kernel, dev);
+  auto it = done.find(key);
+  if (it != done.end() && it->second >= bytes) return 0;
+  if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return GXA_ERR_CUDA;
+  done[key] = bytes;
+  return 0;
+}
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+void set_error_text(const char* msg) { strncpy(g_err, msg, sizeof(g_err) - 1); g_err[sizeof(g_err) - 1] = 0; }
 // Measured at c3 (D = 1024, 24 layers, one B200): staging the next kernel early hides ~1.2 ms of launch gaps per step
 // whatever the batch, but costs ~0.7% of the kernel time -> a gain below ~40 samples x 448 rows per GPU (-7% at 8, -4.7%
 // at 16, -0.6% at 32) and a loss above (+0.7% at 64).  GXA_PDL=0 / 1 forces it off / on.
@@ -26,16 +44,16 @@ bool pdl_enabled() {
 }
 static std::atomic<int> g_sm_limit{0};   // gxa_set_sm_limit: SMs the persistent grids may assume (0 = all)
 int num_sms() {
-  if (g_sms == 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-      g_sms = n;
-    else
-      g_sms = 148;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) dev = 0;
+  int sms = g_sms_dev[dev].load(std::memory_order_relaxed);
+  if (sms == 0) {
+    int n = 0;
+    sms = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
+    g_sms_dev[dev].store(sms, std::memory_order_relaxed);
   }
   const int lim = g_sm_limit.load(std::memory_order_relaxed);
-  return lim > 0 && lim < g_sms ? lim : g_sms;
+  return lim > 0 && lim < sms ? lim : sms;
 }
 static int fail(int code) {
   cudaError_t e = cudaPeekAtLastError();
@@ -194,6 +212,7 @@ struct SideStream {
   cudaStream_t s = nullptr;
   cudaEvent_t fork[8] = {};
   cudaEvent_t join = nullptr;
+  cudaEvent_t early = nullptr;      // a point in the middle of the side stream's work the caller's stream waits for
   bool ok = false;
 };
 static SideStream* side_stream() {
@@ -203,11 +222,13 @@ static SideStream* side_stream() {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
   SideStream& sd = per_dev[dev];
+  std::lock_guard<std::mutex> lk(g_init_mu);
   if (!sd.ok) {
     if (cudaStreamCreateWithFlags(&sd.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     for (auto& e : sd.fork)
       if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     if (cudaEventCreateWithFlags(&sd.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&sd.early, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     sd.ok = true;
   }
   return &sd;
@@ -319,10 +340,20 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   WCache W(d, wcache);
   if (cudaMemsetAsync(Wk.gacc, 0, 64 * sizeof(float), s) != cudaSuccess) return fail(GXA_ERR_CUDA);
   SideStream* sd = side_stream();    // weight gradients leave the dgrad chain (joined before returning)
+  // the fp32 dQ accumulator of the attention backward (134 MB at c3) is zeroed on the side stream, under the FFN
+  // backward GEMMs (tensor-bound: HBM is idle there), instead of in front of the attention kernel
+  bool dq_zeroed = false;
+  if (sd && d.has_xa) {
+    const cudaStream_t zs = side_fork(sd, 4, s);
+    if (zs != s && cudaMemsetAsync(Wk.dqacc, 0, attn_bwd_workspace_bytes(d.B, d.H, d.Lq), zs) == cudaSuccess &&
+        cudaEventRecord(sd->early, zs) == cudaSuccess)
+      dq_zeroed = true;
+  }
   const float* x1 = d.has_xa ? S.x1 : x;
   // ---- FFN branch
+  unsigned* fin = reinterpret_cast<unsigned*>(Wk.gacc + 8);      // last-block-done counters of the fused gate finish
   GXA_TRY(gate_bwd(dy, S.f, 0, p.ff_gate, Wk.gacc + 1, Wk.df, 0, g.ff2_b, M, D, s,
-                   make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn)));
+                   make_drop_cfg(d.p_drop, d.seed, kDropStreamFfn), g.ff_gate, fin + 1));
   GXA_TRY(gemm_bf16(Wk.df, D, false, W.ff2, 4 * D, true, M, 4 * D, D, EPI_GELU_BWD, Wk.du, 4 * D, nullptr, 0, nullptr,
                     S.u, 4 * D, nullptr, 0, s, g.ff0_b));     // d(ff.0.bias) = colsum(du) fused in the epilogue
   GXA_TRY(gemm_bf16(Wk.df, D, true, S.a, 4 * D, true, D, 4 * D, M, EPI_F32, g.ff2_w, 4 * D, nullptr, 0, nullptr, nullptr,
@@ -331,29 +362,29 @@ static int block_bwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
                     nullptr, 0, s));
   GXA_TRY(gemm_bf16(Wk.du, 4 * D, true, S.h2, D, true, 4 * D, D, M, EPI_F32, g.ff0_w, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 1, side_fork(sd, 1, s)));
-  GXA_TRY(gate_finish(p.ff_gate, Wk.gacc + 1, g.ff_gate, s));
   if (!d.has_xa) {
     GXA_TRY(ln_bwd(Wk.dh2, 0, x1, p.ff_ln_w, S.mean2, S.rstd2, dy, dx, g.ff_ln_w, g.ff_ln_b, nullptr, 0, nullptr, nullptr,
                    nullptr, nullptr, M, D, s));
     return side_join(sd, s);
   }
-  // ---- LN2 backward fused with the attention-gate backward: dx1, do = tanh(a)*dx1, d(attn_gate), d(bo)
+  // ---- LN2 backward fused with the attention-gate backward: dx1, do = tanh(a)*dx1, d(attn_gate) (finished by the
+  // kernel's last block), d(bo)
   GXA_TRY(ln_bwd(Wk.dh2, 0, x1, p.ff_ln_w, S.mean2, S.rstd2, dy, Wk.dx1, g.ff_ln_w, g.ff_ln_b, S.o, 0, p.attn_gate,
-                 Wk.gacc, Wk.dob, g.out_proj_b, M, D, s));
-  GXA_TRY(gate_finish(p.attn_gate, Wk.gacc, g.attn_gate, s));
+                 Wk.gacc, Wk.dob, g.out_proj_b, M, D, s, g.attn_gate, fin));
   GXA_TRY(gemm_bf16(Wk.dob, D, false, W.out, D, true, M, D, D, EPI_BF16, Wk.dctx, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 0, s));
   GXA_TRY(gemm_bf16(Wk.dob, D, true, S.ctx, D, true, D, D, M, EPI_F32, g.out_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
                     nullptr, 1, side_fork(sd, 2, s)));
   // ---- attention core
+  if (dq_zeroed && cudaStreamWaitEvent(s, sd->early, 0) != cudaSuccess) return fail(GXA_ERR_CUDA);
+  // fused into the attention backward: d(bq) (column sums of dq, in the finalize kernel) and d(bv) (column sums of dV, in
+  // the drain warps).  d(bk) is identically zero (every row of dS sums to zero -- softmax is invariant to a per-query
+  // shift of the logits; the reference's autograd returns rounding noise there) and is left at zero.
   GXA_TRY(attn_bwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, Wk.dctx, D, S.lse, Wk.delta, Wk.dq, D,
-                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s, g.in_proj_b,      // + fused d(bq)
-                        make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
+                        Wk.dkv, Wk.dkv + D, 2 * D, Wk.dqacc, d.B, d.H, d.Lq, d.Lk, s, g.in_proj_b,
+                        make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn), g.in_proj_b + 2 * D, dq_zeroed));
   {   // everything that only consumes dq / dkv and is not on the way to dx: side stream
     const cudaStream_t ws = side_fork(sd, 3, s);
-    // d(bv) only: d(bk) is identically zero (every row of dS sums to zero -- softmax is invariant to a per-query shift
-    // of the logits; the reference's autograd returns rounding noise there), so the K half is not read
-    GXA_TRY(colsum(Wk.dkv + D, 0, 2 * D, g.in_proj_b + 2 * D, Mk, D, ws));
     GXA_TRY(gemm_bf16(Wk.dq, D, true, S.h, D, true, D, D, M, EPI_F32, g.in_proj_w, D, nullptr, 0, nullptr, nullptr, 0,
                       nullptr, 1, ws));
     GXA_TRY(gemm_bf16(Wk.dkv, 2 * D, true, xa_op, D, true, 2 * D, D, Mk, EPI_F32, g.in_proj_w + size_t(D) * D, D, nullptr,

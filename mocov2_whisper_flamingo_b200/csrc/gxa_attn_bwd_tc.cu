@@ -77,7 +77,8 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                     const __grid_constant__ CUtensorMap tmDO, const uint8_t* __restrict__ mask,
                     const int* __restrict__ kv_end, const float* __restrict__ lse, const float* __restrict__ delta,
                     float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dk, __nv_bfloat16* __restrict__ dv, int lddkv,
-                    int B, int H, int Lq, int Lk, int D, int LqPad, const DropCfg drop, long long* dbg) {
+                    int B, int H, int Lq, int Lk, int D, int LqPad, const DropCfg drop, float* __restrict__ dv_colsum,
+                    long long* dbg) {
 #ifdef GXA_BWD_STAMPS   // clock stamps of the pipeline events of CTA 0 (tools/dbg_attn_bwd.py); off in the product build
 #define STAMP(role, k) do { if (dbg && blockIdx.x == 0 && g < 16 && lane == 0) dbg[(role) * 128 + g * 8 + (k)] = clock64(); } while (0)
 #else
@@ -476,6 +477,26 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                              pk2(__uint_as_float(a[8 * j + 4]) * scale, __uint_as_float(a[8 * j + 5]) * scale),
                              pk2(__uint_as_float(a[8 * j + 6]) * scale, __uint_as_float(a[8 * j + 7]) * scale));
           }
+          if (t == 0 && dv_colsum != nullptr) {
+            // fused d(bv) = column sums of dV: the tile is in registers here (thread = key row, 32 columns), so the
+            // separate 98 MB pass over d(k|v) per layer is not needed.  Transposing butterfly over the warp's 32 rows
+            // (31 shuffles per 32 columns; lane l ends up with column l), one fp32 atomic per column and warp.  Rows of
+            // padded keys hold exact zeros (P = 0 there), so every row may take part.
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(a[i]);
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) {
+              const bool up = (lane & off) != 0;
+#pragma unroll
+              for (int i = 0; i < off; ++i) {
+                const float send = up ? v[i] : v[i + off];
+                const float keep = up ? v[i + off] : v[i];
+                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+              }
+            }
+            atomicAdd(dv_colsum + cur.h * HD + c + lane, v[0]);
+          }
         }
       }
       // ---- key visibility of item n+2 (its buffer was last read by item n, which is complete)
@@ -546,27 +567,28 @@ size_t attn_bwd_tc_workspace(int B, int H, int Lq);
 // Persistent backward (see the header of this file).  Same contract as attn_bwd_tc.
 int attn_bwd_tc2(const void* q, int ldq, const void* kv, int ldkv, const uint8_t* mask, const int* kv_end,
                  const void* dctx, int ldc, const float* lse, const float* delta, float* dq_acc, void* dq, int lddq,
-                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s, DropCfg drop) {
+                 void* dk, void* dv, int lddkv, int B, int H, int Lq, int Lk, float* dq_colsum, cudaStream_t s, DropCfg drop,
+                 float* dv_colsum, bool acc_is_zero) {
   const int D = H * HD;
   const int LqPad = (Lq + BQ - 1) / BQ * BQ;
   CUtensorMap tmQ, tmKV, tmDO;
   if (int e = make_tmap_bf16_3d(&tmQ, q, D, Lq, B, ldq, size_t(Lq) * ldq, 64, BQ)) return e;
   if (int e = make_tmap_bf16_3d(&tmKV, kv, 2 * D, Lk, B, ldkv, size_t(Lk) * ldkv, 64, BK)) return e;
   if (int e = make_tmap_bf16_3d(&tmDO, dctx, D, Lq, B, ldc, size_t(Lq) * ldc, 64, BQ)) return e;
-  static bool attr = false;
-  if (!attr) {
-    if (cudaFuncSetAttribute(attn_bwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
-      return GXA_ERR_CUDA;
-    attr = true;
-  }
-  if (cudaMemsetAsync(dq_acc, 0, attn_bwd_tc_workspace(B, H, Lq), s) != cudaSuccess) return GXA_ERR_CUDA;
+  if (int e = set_max_smem_once(attn_bwd_tc2_kernel, SMEM_BYTES)) return e;
+  // the fp32 dQ accumulator must start from zero; a caller that zeroed it off the critical path says so
+  if (!acc_is_zero && cudaMemsetAsync(dq_acc, 0, attn_bwd_tc_workspace(B, H, Lq), s) != cudaSuccess) return GXA_ERR_CUDA;
   const int total = B * H * ((Lk + BK - 1) / BK);
   int grid = total < num_sms() ? total : num_sms();
   if ((total + grid - 1) / grid > MAX_ITEMS) grid = (total + MAX_ITEMS - 1) / MAX_ITEMS;
+#ifdef GXA_BWD_STAMPS
   long long* dbg = getenv("GXA_DBG_PTR") ? reinterpret_cast<long long*>(strtoull(getenv("GXA_DBG_PTR"), nullptr, 0)) : nullptr;
+#else
+  long long* dbg = nullptr;      // the stamp hook (tools/dbg_attn_bwd.py) exists in -DGXA_BWD_STAMPS builds only
+#endif
   cudaError_t le = launch_pdl(attn_bwd_tc2_kernel, dim3(grid), dim3(THREADS), SMEM_BYTES, s, tmQ, tmKV, tmDO, mask, kv_end, lse,
                               delta, dq_acc, reinterpret_cast<__nv_bfloat16*>(dk), reinterpret_cast<__nv_bfloat16*>(dv), lddkv,
-                              B, H, Lq, Lk, D, LqPad, drop, dbg);
+                              B, H, Lq, Lk, D, LqPad, drop, dv_colsum, dbg);
   count_launch();
   if (le != cudaSuccess || cudaGetLastError() != cudaSuccess) return GXA_ERR_CUDA;
   le = launch_pdl(attn_dq_finalize2_kernel, dim3(B * H * (LqPad / BQ)), dim3(256), 0, s, dq_acc,

@@ -233,12 +233,7 @@ static int launch_inst(const GemmOp& op, const GemmParams& p, cudaStream_t strea
   else       e = make_tmap_bf16(&tmB, op.B, op.N, op.K, op.ldb, 64, GEMM_BK);
   if (e) return e;
   auto kern = gemm_tc_kernel<BN, EPI, A_MN, B_MN>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES) != cudaSuccess)
-      return GXA_ERR_CUDA;
-    attr_set = true;
-  }
+  if (int ae = set_max_smem_once(kern, Cfg::SMEM_BYTES)) return ae;
   const int num_m = (p.M + GEMM_BM - 1) / GEMM_BM, num_n = (p.N + BN - 1) / BN;
   const int total = num_m * num_n * p.k_splits;
   const int grid = total < num_sms() ? total : num_sms();

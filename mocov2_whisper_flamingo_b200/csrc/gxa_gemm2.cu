@@ -247,12 +247,7 @@ static int launch2_inst(const GemmOp& op, const GemmParams& p, cudaStream_t stre
       make_tmap_f32_2d(&tmC, p.C, p.N, p.M, p.ldc, 32, 32) == 0)
     tma_c = 1;
   auto kern = gemm_tc2_kernel<EPI, A_MN, B_MN, STG>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<EPI, STG>::SMEM_BYTES) != cudaSuccess)
-      return GXA_ERR_CUDA;
-    attr_set = true;
-  }
+  if (int ae = set_max_smem_once(kern, G2Cfg<EPI, STG>::SMEM_BYTES)) return ae;
   const int num_m = (p.M + G2_BM - 1) / G2_BM, num_n = (p.N + G2_BN - 1) / G2_BN;
   const int total = num_m * num_n * p.k_splits;
   const int max_pairs = num_sms() / 2;

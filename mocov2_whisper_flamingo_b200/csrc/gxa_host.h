@@ -17,6 +17,11 @@ typedef CUresult (*PFN_cuTensorMapEncodeTiled_t)(CUtensorMap*, CUtensorMapDataTy
 
 int num_sms();
 void count_launch();
+void set_error_text(const char* msg);      // text returned by gxa_last_cuda_error() for the next failure
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per (kernel, device): set once for each pair (thread-safe)
+int set_max_smem_once_impl(const void* kernel, int bytes);
+template <typename K>
+inline int set_max_smem_once(K kernel, int bytes) { return set_max_smem_once_impl(reinterpret_cast<const void*>(kernel), bytes); }
 
 // Programmatic dependent launch: the kernel may be scheduled while its predecessor on the stream is still running, so
 // its prologue (barrier init, TMEM allocation, tensor-map prefetch) and the launch latency overlap the predecessor's
@@ -73,10 +78,12 @@ int ln_fwd(const float* x, const float* w, const float* b, void* out, int out_is
 //   dgate_accum += sum(dx * o),  dout(bf16 or f32) = tanh(gate) * dx,  dbias_out += colsum(dout)
 int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const float* mean, const float* rstd,
            const float* dres, float* dx, float* dw, float* db, const void* o, int o_is_f32, const float* gate,
-           float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s);
+           float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s,
+           float* dgate_out = nullptr, unsigned* done_counter = nullptr);   // fused gate_finish (last block; counter zeroed by the caller)
 // dout = tanh(gate) * dy ; dgate_accum += sum(dy * f) ; dbias += colsum(dout)
 int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, float* dgate_accum, void* dout,
-             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s, DropCfg drop = DropCfg{0, 1.f, 0, 0});
+             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s, DropCfg drop = DropCfg{0, 1.f, 0, 0},
+             float* dgate_out = nullptr, unsigned* done_counter = nullptr);   // fused gate_finish, as in ln_bwd
 int gate_finish(const float* gate, const float* accum, float* dgate, cudaStream_t s);   // dgate = (1-tanh^2) * accum
 int colsum(const void* src, int is_f32, int ld, float* dst, int rows, int cols, cudaStream_t s);   // dst += colsum
 int cast_f32_bf16(const float* src, void* dst, size_t n, cudaStream_t s);
@@ -100,8 +107,10 @@ int attn_fwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv
 int attn_bwd_bf16(const void* q, int ldq, const void* k, const void* v, int ldkv, const uint8_t* mask, const int* kv_end,
                   const void* ctx, const void* dctx, int ldc, const float* lse, float* delta, void* dq, int lddq,
                   void* dk, void* dv, int lddkv, void* workspace, int B, int H, int Lq, int Lk, cudaStream_t s,
-                  float* dq_colsum = nullptr,    // optional: += column sums of dq (fused bias gradient)
-                  DropCfg drop = DropCfg{0, 1.f, 0, 0});
+                  float* dq_colsum = nullptr,    // optional: += column sums of dq (fused bias gradient d bq)
+                  DropCfg drop = DropCfg{0, 1.f, 0, 0},
+                  float* dv_colsum = nullptr,    // optional: += column sums of dv (fused bias gradient d bv)
+                  bool acc_is_zero = false);     // the fp32 dQ accumulator in `workspace` was zeroed by the caller
 size_t attn_bwd_workspace_bytes(int B, int H, int Lq);
 int attn_fwd_f32(const float* q, int ldq, const float* k, const float* v, int ldkv, const uint8_t* mask, float* ctx,
                  int ldc, float* P, int B, int H, int Lq, int Lk, cudaStream_t s, DropCfg drop = DropCfg{0, 1.f, 0, 0});

@@ -124,6 +124,24 @@ __device__ __forceinline__ void flush_cols(float4 (&acc)[NV], float* __restrict_
   }
 }
 
+// d(gate) = (1 - tanh^2(gate)) * accum, written by the LAST block of the kernel that produced `accum` (no separate
+// one-thread launch per gate: 48 launches per step at c3).  Every warp has added its partial to *accum before the
+// block-wide barrier; the block then counts itself in, and the block that sees the full count reads the total.
+__device__ __forceinline__ void gate_finish_last_block(const float* gate, float* accum, float* dgate_out, unsigned* counter) {
+  if (dgate_out == nullptr) return;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned total = gridDim.x * gridDim.y;
+    if (atomicAdd(counter, 1u) == total - 1) {
+      __threadfence();
+      const float acc = atomicAdd(accum, 0.f);         // coherent read of the finished sum
+      const float t = tanhf(__ldg(gate));
+      dgate_out[0] += (1.0f - t * t) * acc;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ LayerNorm backward (+ gate backward)
 template <int NV, bool GATED>
 __global__ void __launch_bounds__(RW_WARPS * 32)
@@ -206,7 +224,7 @@ ln_bwd_split_kernel(const void* __restrict__ g, int g_is_f32, const float* __res
                     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ dres,
                     float* __restrict__ dx, float* __restrict__ dw, float* __restrict__ db, const void* __restrict__ o,
                     int o_is_f32, const float* __restrict__ gate, float* __restrict__ dgate_accum, void* __restrict__ dout,
-                    float* __restrict__ dbias_out, int rows) {
+                    float* __restrict__ dbias_out, int rows, float* __restrict__ dgate_out, unsigned* __restrict__ done_counter) {
   pdl_launch_dependents();
   pdl_wait();
   constexpr int D = 128 * NVW * W;
@@ -294,6 +312,7 @@ ln_bwd_split_kernel(const void* __restrict__ g, int g_is_f32, const float* __res
     flush(ao, dbias_out);
     gacc = warp_sum(gacc);
     if (lane == 0) atomicAdd(dgate_accum, gacc);
+    gate_finish_last_block(gate, dgate_accum, dgate_out, done_counter);
   }
 }
 
@@ -311,7 +330,7 @@ template <int NVW, int W>
 static int ln_bwd_split_launch(const void* g, int g_is_f32, const float* x, const float* w, const float* mean,
                                const float* rstd, const float* dres, float* dx, float* dw, float* db, const void* o,
                                int o_is_f32, const float* gate, float* dgate_accum, void* dout, float* dbias_out, int rows,
-                               cudaStream_t s) {
+                               cudaStream_t s, float* dgate_out, unsigned* done_counter) {
   constexpr int D = 128 * NVW * W, GROUPS = RW_WARPS / W;
   const size_t smem = sizeof(float) * GROUPS * D;
   if (o != nullptr) {
@@ -321,7 +340,7 @@ static int ln_bwd_split_launch(const void* g, int g_is_f32, const float* x, cons
     const int grid_cap = per_sm * num_sms();
     const int blocks = (rows + GROUPS - 1) / GROUPS;
     launch_pdl(k, dim3(blocks < grid_cap ? blocks : grid_cap), dim3(RW_WARPS * 32), smem, s, g, g_is_f32, x, w, mean, rstd, dres,
-               dx, dw, db, o, o_is_f32, gate, dgate_accum, dout, dbias_out, rows);
+               dx, dw, db, o, o_is_f32, gate, dgate_accum, dout, dbias_out, rows, dgate_out, done_counter);
   } else {
     auto k = ln_bwd_split_kernel<NVW, W, false>;
     static int per_sm = 0;
@@ -329,7 +348,7 @@ static int ln_bwd_split_launch(const void* g, int g_is_f32, const float* x, cons
     const int grid_cap = per_sm * num_sms();
     const int blocks = (rows + GROUPS - 1) / GROUPS;
     launch_pdl(k, dim3(blocks < grid_cap ? blocks : grid_cap), dim3(RW_WARPS * 32), smem, s, g, g_is_f32, x, w, mean, rstd, dres,
-               dx, dw, db, nullptr, 0, nullptr, nullptr, nullptr, nullptr, rows);
+               dx, dw, db, nullptr, 0, nullptr, nullptr, nullptr, nullptr, rows, nullptr, nullptr);
   }
   return check_launch();
 }
@@ -342,12 +361,14 @@ static inline int rowwise_grid(int rows) {
 
 int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const float* mean, const float* rstd,
            const float* dres, float* dx, float* dw, float* db, const void* o, int o_is_f32, const float* gate,
-           float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s) {
+           float* dgate_accum, void* dout, float* dbias_out, int rows, int D, cudaStream_t s, float* dgate_out,
+           unsigned* done_counter) {
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
+  if (o == nullptr) dgate_out = nullptr;
 #define GXA_LN_SPLIT(NVW, W) \
   return ln_bwd_split_launch<NVW, W>(g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, o, o_is_f32, gate, dgate_accum, dout, \
-                                     dbias_out, rows, s)
+                                     dbias_out, rows, s, dgate_out, done_counter)
   switch (D / 128) {
     case 8: GXA_LN_SPLIT(2, 4);
     case 4: GXA_LN_SPLIT(1, 4);
@@ -368,7 +389,9 @@ int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const fl
                            g, g_is_f32, x, w, mean, rstd, dres, dx, dw, db, nullptr, 0, nullptr, nullptr, nullptr,
                            nullptr, rows)));
   }
-  return check_launch();
+  if (int e = check_launch()) return e;
+  // the one-warp-per-row kernel (widths without a row split) has no fused finish
+  return (o != nullptr && dgate_out != nullptr) ? gate_finish(gate, dgate_accum, dgate_out, s) : 0;
 }
 
 // ------------------------------------------------------------------ gate backward (FFN side)
@@ -377,7 +400,7 @@ template <int NV>
 __global__ void __launch_bounds__(RW_WARPS * 32)
 gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_is_f32, const float* __restrict__ gate,
                 float* __restrict__ dgate_accum, void* __restrict__ dout, int out_is_f32, float* __restrict__ dbias,
-                int rows, const DropCfg drop) {
+                int rows, const DropCfg drop, float* __restrict__ dgate_out, unsigned* __restrict__ done_counter) {
   pdl_launch_dependents();
   pdl_wait();
   constexpr int D = 128 * NV;
@@ -415,17 +438,19 @@ gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_
   flush_cols<NV>(ao, dbias, sm);
   gacc = warp_sum(gacc);
   if (lane == 0) atomicAdd(dgate_accum, gacc);
+  gate_finish_last_block(gate, dgate_accum, dgate_out, done_counter);
 }
 
 int gate_bwd(const float* dy, const void* f, int f_is_f32, const float* gate, float* dgate_accum, void* dout,
-             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s, DropCfg drop) {
+             int out_is_f32, float* dbias, int rows, int D, cudaStream_t s, DropCfg drop, float* dgate_out,
+             unsigned* done_counter) {
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
   const size_t smem = sizeof(float) * RW_WARPS * D;
   int grid = 1;
   GXA_NV_DISPATCH(D, (grid = resident_grid(gate_bwd_kernel<NV>, smem, rows, RW_WARPS)));
   GXA_NV_DISPATCH(D, (launch_pdl(gate_bwd_kernel<NV>, dim3(grid), dim3(RW_WARPS * 32), smem, s, dy, f, f_is_f32, gate, dgate_accum, dout,
-                                 out_is_f32, dbias, rows, drop)));
+                                 out_is_f32, dbias, rows, drop, dgate_out, done_counter)));
   return check_launch();
 }
 

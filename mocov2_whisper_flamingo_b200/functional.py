@@ -83,18 +83,39 @@ class BlockState:
     def __init__(self):
         self.wcache = None
         self.key = None
+        self.ready = None        # event of a cast enqueued on another stream (prefetch), not yet waited for
+        self._event = None
 
-    def refresh(self, dims: Dims, params, pp: BlockPtrs) -> torch.Tensor:
+    @staticmethod
+    def _key(dims: Dims, params):
+        return (dims.precision, dims.D) + tuple((p.data_ptr(), p._version) for p in params)
+
+    def refresh(self, dims: Dims, params, pp: BlockPtrs, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """(Re)build the bf16 operand cache if a weight changed.  With ``stream`` the cast is enqueued there (the stack
+        prefetches every layer's cast off the critical path) and ``wait_ready()`` orders the consumer after it."""
         L = _lib.lib()
-        key = (dims.precision, dims.D) + tuple((p.data_ptr(), p._version) for p in params)
+        key = self._key(dims, params)
         if self.wcache is None or self.key != key:
             n = L.gxa_block_wcache_bytes(C.byref(dims))
             if self.wcache is None or self.wcache.numel() != n:
                 self.wcache = torch.empty(n, dtype=torch.uint8, device=params[0].device)
-            check(L.gxa_block_prepare_weights(C.byref(dims), C.byref(pp), self.wcache.data_ptr(), _stream()),
+            check(L.gxa_block_prepare_weights(C.byref(dims), C.byref(pp), self.wcache.data_ptr(),
+                                              stream.cuda_stream if stream is not None else _stream()),
                   "gxa_block_prepare_weights")
             self.key = key
+            if stream is not None:
+                if self._event is None:
+                    self._event = torch.cuda.Event()
+                self._event.record(stream)
+                self.ready = self._event
+            else:
+                self.ready = None
         return self.wcache
+
+    def wait_ready(self) -> None:
+        if self.ready is not None:
+            torch.cuda.current_stream().wait_event(self.ready)
+            self.ready = None
 
 
 class StackShared:
@@ -173,6 +194,7 @@ class BlockFn(torch.autograd.Function):
                                    "supported storage, SURVEY A.1 M8)")
         pp = BlockPtrs(*[p.data_ptr() for p in pd])
         wcache = state.refresh(dims, pd, pp)
+        state.wait_ready()
         if has_xa and shared.xa_op is None:
             n = L.gxa_xa_operand_bytes(C.byref(dims))
             shared.xa_op = torch.empty(n, dtype=torch.uint8, device=x.device)

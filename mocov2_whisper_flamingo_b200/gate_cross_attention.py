@@ -23,7 +23,8 @@ from typing import Optional
 import torch
 import torch.nn as nn
 
-from .functional import (BlockFn, BlockState, LayerNormFn, LinearFn, StackShared, resolve_precision,
+from ._lib import BlockPtrs, GXA_PREC_BF16
+from .functional import (BlockFn, BlockState, LayerNormFn, LinearFn, StackShared, _dims, resolve_precision,
                          set_default_precision)
 
 logger = logging.getLogger(__name__)
@@ -103,6 +104,7 @@ class GatedCrossModalFusion(nn.Module):
         self.ln_post = LayerNorm(d_model)
         self.precision: Optional[int] = None
         self.grad_hook = None    # set by parallel.DataParallelGrads: per-layer gradient all-reduce
+        self._cast_streams = {}  # device index -> stream the weight casts are prefetched on
 
     def invalidate_weight_cache(self):
         """Force the bf16 operand cache of every layer to be rebuilt on the next forward (the cache is
@@ -110,9 +112,34 @@ class GatedCrossModalFusion(nn.Module):
         for layer in self.layers:
             layer._state.key = None
 
+    def _prefetch_weight_casts(self, prec: int, device: torch.device) -> None:
+        """bf16 mode: the fp32 -> bf16 operand cast of every layer whose weights changed since the last call (all of them
+        after an optimizer step) is enqueued on a side stream at the start of the stack, ordered after the work already on
+        the caller's stream (the weight update), instead of in front of each layer's first GEMM: 24 HBM-bound passes of
+        75 MB leave the critical path (1.25 ms of a 15 ms step at 8 samples per GPU)."""
+        if prec != GXA_PREC_BF16 or device.type != "cuda":
+            return
+        stale = []
+        for layer in self.layers:
+            pd = [p.detach() for p in layer._params()]
+            dims = _dims(1, 1, 1, layer.d_model, layer.n_heads, prec, True)
+            if layer._state.wcache is None or layer._state.key != BlockState._key(dims, pd):
+                stale.append((layer, dims, pd))
+        if not stale:
+            return
+        side = self._cast_streams.get(device.index)
+        if side is None:
+            side = self._cast_streams[device.index] = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        for layer, dims, pd in stale:
+            if any(p.dtype != torch.float32 or not p.is_contiguous() or not p.is_cuda for p in pd):
+                return                     # BlockFn.forward raises the proper error
+            layer._state.refresh(dims, pd, BlockPtrs(*[p.data_ptr() for p in pd]), stream=side)
+
     def forward(self, audio_features, video_features, audio_mask=None, video_mask=None):
         _log_shapes(self.enable_logging, "fusion in", audio_features=audio_features, video_features=video_features)
         prec = resolve_precision(self.precision)
+        self._prefetch_weight_casts(prec, audio_features.device)
         x = LinearFn.apply(audio_features, self.audio_proj.weight, self.audio_proj.bias, prec)
         xa = LinearFn.apply(video_features, self.video_proj.weight, self.video_proj.bias, prec)
         _log_shapes(self.enable_logging, "fusion projected", x=x, xa=xa)

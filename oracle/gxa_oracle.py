@@ -224,6 +224,10 @@ def block_backward(p, c, dy):
     flat = lambda t: t.reshape(-1, t.shape[-1])
     gf = c["gf"]
     g["ff_gate"] = np.array([(1 - gf * gf) * (dy * c["f"]).sum()])
+    # A gate gradient is ONE scalar: the sum of B*Lq*D signed terms.  Its natural magnitude is the 2-norm of the terms
+    # (what a random-sign sum of them has); the total itself can be cancelled far below that, which makes "relative to
+    # the total" an ill-conditioned yardstick for a single number.  Kept beside the gradients for the parity tests.
+    c["gate_scale"] = {"ff_gate": (1 - gf * gf) * float(np.sqrt(((dy * c["f"]) ** 2).sum()))}
     df = gf * dy
     if c.get("ffn_m") is not None:
         df = df * c["ffn_m"]
@@ -243,6 +247,7 @@ def block_backward(p, c, dy):
         return g, dx1, None
     ga = c["ga"]
     g["attn_gate"] = np.array([(1 - ga * ga) * (dx1 * c["o"]).sum()])
+    c["gate_scale"]["attn_gate"] = (1 - ga * ga) * float(np.sqrt(((dx1 * c["o"]) ** 2).sum()))
     do = ga * dx1
     g["attn.out_proj.weight"] = flat(do).T @ flat(c["ctx"])
     g["attn.out_proj.bias"] = flat(do).sum(0)
@@ -304,6 +309,13 @@ def fusion_backward(p, c, dy):
     d_audio = dx @ _f64(p["audio_proj.weight"])
     d_video = dxa @ _f64(p["video_proj.weight"])
     return g, d_audio, d_video
+
+
+def gate_scales(c) -> dict:
+    """name -> 2-norm of the terms a gate gradient sums (after block_backward / fusion_backward ran on cache c)."""
+    if "caches" in c:
+        return {f"layers.{i}.{k}": v for i, ci in enumerate(c["caches"]) for k, v in ci.get("gate_scale", {}).items()}
+    return dict(c.get("gate_scale", {}))
 
 
 def rel_err(a, b):

@@ -21,6 +21,15 @@ def rel_err(a, b):
     return (a - b).abs().max().item() / (den if den > 0 else 1.0)
 
 
+def scalar_sum_err(mine, ref, scale):
+    """Error of a scalar that is a sum of many signed terms (the two gate gradients), relative to
+    max(|ref|, 2-norm of the terms): the natural size of such a sum.  The total itself may be cancelled far below it, and
+    a relative error against a cancelled total says nothing about the kernels (the reference's own bf16-autocast run is
+    1.7e-2 off its fp32 run on such a scalar)."""
+    mine, ref = float(mine), float(ref)
+    return abs(mine - ref) / max(abs(ref), float(scale), 1e-30)
+
+
 def err_map(a, b, br=32, bc=32):
     """coarse map of where two matrices disagree (for diagnosing tile/descriptor bugs from one run)"""
     d = (a.double() - b.double()).abs()

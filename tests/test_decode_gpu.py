@@ -99,4 +99,6 @@ def test_decode_at_config5_shape_matches_cpu_reference():
     assert rel_err(y_full.cpu(), yr) < 2e-2
     assert rel_err(y_eager.cpu(), yr) < 2e-2
     assert rel_err(y_graph.cpu(), yr) < 2e-2
-    assert rel_err(y_graph, y_eager) < 1e-5
+    # eager vs graph replay: the split-K gated residuals add their partials with fp32 atomics in arrival order; through
+    # 12 layers a 1e-7 difference can flip a bf16 rounding downstream (one bf16 ulp = 4e-3 of that element)
+    assert rel_err(y_graph, y_eager) < 5e-3

@@ -120,3 +120,25 @@ def test_f64_restatement_matches_avnet_fixture():
         if k.endswith("in_proj_bias"):
             continue                                  # bk third is fp32 noise in the reference (checked above per block)
         assert O.rel_err(gr[k], g["grad/" + k]) < 5e-5, k
+
+
+def test_gate_gradient_scales_agree_between_the_two_checkers():
+    """The parity tests measure the two scalar gate gradients against the 2-norm of the terms they sum (gpu_util.
+    scalar_sum_err); both checkers must produce the same scale, and the total is never larger than sqrt(N) times it."""
+    import torch
+    from oracle import torch_port as TP
+    D, H, nl, seed = 128, 2, 2, 5
+    p = O.make_params(O.fusion_param_shapes(D, nl), seed)
+    x, xa, mask, dy = O.make_inputs(2, 12, 20, D, seed, [20, 7])
+    y, c = O.fusion_forward(p, x, xa, mask, H, nl)
+    g, _, _ = O.fusion_backward(p, c, dy)
+    so = O.gate_scales(c)
+    pt = TP.to_torch(p, requires_grad=True)
+    taps = []
+    yt = TP.fusion_forward(pt, torch.from_numpy(x), torch.from_numpy(xa), torch.from_numpy(mask), H, nl, taps=taps)
+    yt.backward(torch.from_numpy(dy))
+    st = TP.gate_scales(pt, taps)
+    assert set(so) == set(st) == {f"layers.{i}.{k}" for i in range(nl) for k in ("attn_gate", "ff_gate")}
+    for k in so:
+        assert abs(so[k] - st[k]) / so[k] < 1e-4, (k, so[k], st[k])
+        assert abs(float(g[k][0])) <= so[k] * (2 * 12 * D) ** 0.5 * (1 + 1e-9)

@@ -6,8 +6,8 @@ import sys
 
 import torch
 
-sys.path.insert(0, __file__.rsplit("/tests/", 1)[0])
-sys.path.insert(0, __file__.rsplit("/", 1)[0])
+sys.path.insert(0, __file__.rsplit("/tools/", 1)[0])
+sys.path.insert(0, __file__.rsplit("/tools/", 1)[0] + "/tests")
 from mocov2_whisper_flamingo_b200 import _lib  # noqa: E402
 from gpu_util import ptr, stream  # noqa: E402
 
