@@ -43,7 +43,7 @@ typedef struct gxa_dims {
   /* training-mode dropout (models/gate_cross_attention.py:16 nn.MultiheadAttention(dropout=p) -> on the attention
    * probabilities; :26 nn.Dropout(p) after ff.2).  p_drop = 0 disables it (eval mode).  The masks are a pure
    * function of (seed, element) -- csrc/gxa_rng.cuh -- so forward and backward must be called with the same seed;
-   * give every (step, layer) its own seed.  bf16 precision only. */
+   * give every (step, layer) its own seed.  Both precisions.  Drop probability = round(p * 32768) / 32768, p <= 0.968. */
   float p_drop;
   uint32_t reserved2;
   uint64_t seed;

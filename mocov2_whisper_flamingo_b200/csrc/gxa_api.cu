@@ -468,12 +468,10 @@ int gxa_dropout_multipliers_host(float p_drop, uint64_t seed, int site, int rows
   if (!out || rows < 0 || cols < 0) return GXA_ERR_ARG;
   if (!(p_drop >= 0.f && p_drop < 1.f) || (site != int(kDropStreamAttn) && site != int(kDropStreamFfn))) return GXA_ERR_ARG;
   const DropCfg c = make_drop_cfg(p_drop, seed, uint32_t(site));
-  const uint32_t half = uint32_t(cols + 1) >> 1, t = c.thresh << 16;
+  const uint32_t quarter = uint32_t(cols + 3) >> 2;
   for (int r = 0; r < rows; ++r)
     for (int col = 0; col < cols; ++col) {
-      if (c.thresh == 0) { out[size_t(r) * cols + col] = 1.f; continue; }
-      const uint32_t x = drop_mix(uint32_t(r) * half + (uint32_t(col) >> 1), c.seed_lo, c.seed_hi);   // gxa_rng.cuh
-      const bool keep = (col & 1) ? x >= t : (x << 16) >= t;
+      const bool keep = c.thresh == 0 || drop_keep_scalar(c, uint32_t(r) * quarter + (uint32_t(col) >> 2), col & 3);   // gxa_rng.cuh
       out[size_t(r) * cols + col] = keep ? c.scale : 0.f;
     }
   return 0;

@@ -296,8 +296,12 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         // half is loaded and computed, so the working set stays below the 80-register cap of this 704-thread CTA
         // (one 32-column pass needed 64 raw + 32 result registers and spilled ~40 local-memory accesses per iteration,
         // which go through the same L1/shared-memory pipe the MMA operands are fetched from)
-        const float nls = -ls * kLog2e;
-        const float2 c2 = make_float2(kScaleLog2, kScaleLog2), nls2 = make_float2(nls, nls), nde2 = make_float2(-de, -de);
+        // dropout (forward: ctx = (m * P) V with m in {0, 1/(1-p)}): the factor 1/(1-p) rides in the exponent, so
+        //   pe = P / (1-p),  P~ = bf16(pe) & mask (the A operand of dV, exactly what the forward multiplied V with),
+        //   dS = P * (m * dP - delta) = P~ * dP - pe * (delta * (1-p))
+        const float nls = -ls * kLog2e + (drop.thresh != 0 ? log2f(drop.scale) : 0.f);
+        const float nde = drop.thresh != 0 ? -de / drop.scale : -de;
+        const float2 c2 = make_float2(kScaleLog2, kScaleLog2), nls2 = make_float2(nls, nls), nde2 = make_float2(nde, nde);
         uint32_t ppk[16], dpk[16];
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
@@ -311,31 +315,34 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             if (lane == 0) mbar_arrive(&sm.sdp_free);
             if (warp == 0) STAMP(1, 6);
           }
-          uint32_t ctr = 0;
-          if (drop.thresh != 0)           // dropout counter of (row, key pair): same function as the forward (gxa_rng.cuh)
-            ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) * static_cast<uint32_t>((Lk + 1) >> 1) +
-                  ((cur.k0 + cq * 32 + hf * 16) >> 1);
+          uint32_t ctr = 0;               // same function of (row, key) as the forward (gxa_rng.cuh): 4 keys per counter
+          if (drop.thresh != 0)
+            ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) * static_cast<uint32_t>((Lk + 3) >> 2) +
+                  ((cur.k0 + cq * 32 + hf * 16) >> 2);
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {   // packed f32x2 arithmetic (FFMA2 / FMUL2 / FADD2): half the issue slots
-            float2 sv = make_float2(__uint_as_float(sr[2 * c]), __uint_as_float(sr[2 * c + 1]));
-            if (any_masked) sv = __fadd2_rn(sv, *reinterpret_cast<const float2*>(kbias + hf * 16 + 2 * c));
-            const float2 e = __ffma2_rn(sv, c2, nls2);
-            float2 pe = make_float2(ex2a(e.x), ex2a(e.y));
-            const float2 dp = make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1]));
-            float2 ds;
-            if (drop.thresh == 0) {
-              ds = __fmul2_rn(pe, __fadd2_rn(dp, nde2));
-            } else {
-              // dropout on the probabilities (forward: ctx = (m*P) V): dV sees m*P, dP = m * (dO V^T)
-              // dS = P*(m*dP - delta) = (m*P)*dP - P*delta ;  the P tile for dV holds m*P
-              bool k0, k1;
-              drop_keep(drop, ctr + c, k0, k1);
-              const float2 t = __fmul2_rn(pe, nde2);
-              pe = __fmul2_rn(pe, make_float2(k0 ? drop.scale : 0.f, k1 ? drop.scale : 0.f));
-              ds = __ffma2_rn(pe, dp, t);
+          for (int w = 0; w < 4; ++w) {   // one counter = 4 keys = 2 packed pairs
+            uint32_t mk[2] = {0xffffffffu, 0xffffffffu};
+            if (drop.thresh != 0) drop_masks4(drop, ctr + w, mk[0], mk[1]);
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {   // packed f32x2 arithmetic (FFMA2 / FMUL2 / FADD2): half the issue slots
+              const int c = 2 * w + cc;
+              float2 sv = make_float2(__uint_as_float(sr[2 * c]), __uint_as_float(sr[2 * c + 1]));
+              if (any_masked) sv = __fadd2_rn(sv, *reinterpret_cast<const float2*>(kbias + hf * 16 + 2 * c));
+              const float2 e = __ffma2_rn(sv, c2, nls2);
+              const float2 pe = make_float2(ex2a(e.x), ex2a(e.y));
+              const float2 dp = make_float2(__uint_as_float(dr[2 * c]), __uint_as_float(dr[2 * c + 1]));
+              float2 ds;
+              uint32_t pp = pk2(pe.x, pe.y);
+              if (drop.thresh == 0) {
+                ds = __fmul2_rn(pe, __fadd2_rn(dp, nde2));
+              } else {
+                pp &= mk[cc];
+                const float2 pm = make_float2(__uint_as_float(pp << 16), __uint_as_float(pp & 0xffff0000u));
+                ds = __ffma2_rn(pm, dp, __fmul2_rn(pe, nde2));
+              }
+              ppk[hf * 8 + c] = pp;
+              dpk[hf * 8 + c] = pk2(ds.x, ds.y);
             }
-            ppk[hf * 8 + c] = pk2(pe.x, pe.y);
-            dpk[hf * 8 + c] = pk2(ds.x, ds.y);
           }
         }
         if (warp == 0) STAMP(1, 2);

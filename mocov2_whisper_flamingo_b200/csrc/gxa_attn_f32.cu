@@ -30,9 +30,7 @@ __device__ __forceinline__ float dot64(const float* a /*smem*/, const float* __r
 // dropout multiplier (0 or 1/(1-p)) of probability (row, key): the same function of (seed, element) as the bf16 kernels
 __device__ __forceinline__ float drop_mult(const DropCfg& c, uint32_t drop_row, int key) {
   if (c.thresh == 0) return 1.f;
-  float m0, m1;
-  drop_pair(c, drop_row + (static_cast<uint32_t>(key) >> 1), m0, m1);
-  return (key & 1) ? m1 : m0;
+  return drop_keep_scalar(c, drop_row + (static_cast<uint32_t>(key) >> 2), key & 3) ? c.scale : 0.f;
 }
 
 __global__ void __launch_bounds__(128)
@@ -70,7 +68,7 @@ attn_fwd_f32_kernel(const float* __restrict__ q, int ldq, const float* __restric
   for (int j = l; j < Lk; j += 32) pr[j] *= inv;
   __syncwarp();
   float a0 = 0.f, a1 = 0.f;
-  const uint32_t drop_row = static_cast<uint32_t>(row) * static_cast<uint32_t>((Lk + 1) >> 1);   // gxa_rng.cuh counter
+  const uint32_t drop_row = static_cast<uint32_t>(row) * static_cast<uint32_t>((Lk + 3) >> 2);   // gxa_rng.cuh counter
   for (int j = 0; j < Lk; ++j) {
     const float p = pr[j] * drop_mult(drop, drop_row, j);       // P stays undropped in memory (the backward needs both)
     float2 vv = *reinterpret_cast<const float2*>(vb + size_t(j) * ldkv + 2 * l);
@@ -99,7 +97,7 @@ attn_bwd_f32_q_kernel(const float* __restrict__ k, const float* __restrict__ v, 
   const float* pr = P + size_t(row) * Lk;
   float* ds = dS + size_t(row) * Lk;
   float delta = 0.f;
-  const uint32_t drop_row = static_cast<uint32_t>(row) * static_cast<uint32_t>((Lk + 1) >> 1);
+  const uint32_t drop_row = static_cast<uint32_t>(row) * static_cast<uint32_t>((Lk + 3) >> 2);
   for (int j = l; j < Lk; j += 32) {
     const float p = pr[j];
     // forward: ctx = (m * P) V  =>  dP = m * (dO V^T);  delta = rowsum(P * dP) = rowsum(dO * ctx)
@@ -134,7 +132,7 @@ attn_bwd_f32_k_kernel(const float* __restrict__ q, int ldq, const float* __restr
   const float* pb = P + (size_t(b) * H + h) * Lq * Lk + j;
   const float* sb = dS + (size_t(b) * H + h) * Lq * Lk + j;
   float k0 = 0.f, k1 = 0.f, v0 = 0.f, v1 = 0.f;
-  const uint32_t half = static_cast<uint32_t>((Lk + 1) >> 1);
+  const uint32_t half = static_cast<uint32_t>((Lk + 3) >> 2);
   const uint32_t drop_row0 = static_cast<uint32_t>((size_t(b) * H + h) * Lq) * half;
   for (int i = 0; i < Lq; ++i) {
     const float p = pb[size_t(i) * Lk] * drop_mult(drop, drop_row0 + static_cast<uint32_t>(i) * half, j);   // dV sees m * P

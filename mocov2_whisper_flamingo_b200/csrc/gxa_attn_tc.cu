@@ -180,7 +180,8 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
     float m_ref = -INFINITY, l = 0.f;
     const float drop_log2 = drop.thresh != 0 ? log2f(drop.scale) : 0.f;
-    const uint32_t drop_row = (static_cast<uint32_t>(b * H + h) * Lq + (q0 + r)) * static_cast<uint32_t>((Lk + 1) >> 1);
+    // dropout counter of this query row: (b, h, q) * ceil(Lk / 4) + key / 4   (gxa_rng.cuh)
+    const uint32_t drop_row = (static_cast<uint32_t>(b * H + h) * Lq + (q0 + r)) * static_cast<uint32_t>((Lk + 3) >> 2);
 
     for (int j = 0; j < nblk; ++j) {
       const float* kb = sm.kbias + j * TC_BK + half * 64;
@@ -257,19 +258,19 @@ attn_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           la = __fadd2_rn(la, make_float2(pv[i], pv[i + 1]));
           lb = __fadd2_rn(lb, make_float2(pv[i + 2], pv[i + 3]));
         }
-        if (drop.thresh != 0) {      // the row sum above stays undropped (softmax first); dropping is one select per element
-          const uint32_t ctr = drop_row + ((j * TC_BK + half * 64 + c * 32) >> 1);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            bool k0, k1;
-            drop_keep(drop, ctr + i, k0, k1);
-            pv[2 * i] = k0 ? pv[2 * i] : 0.f;
-            pv[2 * i + 1] = k1 ? pv[2 * i + 1] : 0.f;
-          }
-        }
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(pv[2 * i], pv[2 * i + 1]);
+        if (drop.thresh != 0) {      // the row sum above stays undropped (softmax first); dropping = one AND per packed pair
+          const uint32_t ctr = drop_row + ((j * TC_BK + half * 64 + c * 32) >> 2);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            uint32_t m01, m23;
+            drop_masks4(drop, ctr + i, m01, m23);
+            pk[2 * i] &= m01;
+            pk[2 * i + 1] &= m23;
+          }
+        }
         tmem_st_32x16(tmem_p + lane_addr + half * 32 + c * 16, pk);
       }
       l += (la.x + la.y) + (lb.x + lb.y);

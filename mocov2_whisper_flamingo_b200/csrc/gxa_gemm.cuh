@@ -120,13 +120,13 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = bf16r(v[i]);
     if (p.drop.thresh != 0) {
-      const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N >> 1) + (col >> 1);
+      const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N >> 2) + (col >> 2);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        float m0, m1;
-        drop_pair(p.drop, ctr + i, m0, m1);
-        v[2 * i] = bf16r(v[2 * i] * m0);
-        v[2 * i + 1] = bf16r(v[2 * i + 1] * m1);
+      for (int i = 0; i < 8; ++i) {
+        float m[4];
+        drop_mult4(p.drop, ctr + i, m);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[4 * i + j] = bf16r(v[4 * i + j] * m[j]);
       }
     }
     store_bf16x32(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + col, v);
@@ -327,12 +327,13 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
     } else if constexpr (EPI == EPI_GATE_RES) {
       uint2 pk = pack_bf16x4(a);
       a = unpack_bf16x4(pk);
-      if (p.drop.thresh != 0) {      // bf16(linear) -> dropout -> bf16, as autocast does
-        const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N >> 1) + (c >> 1);
-        float m0, m1, m2, m3;
-        drop_pair(p.drop, ctr, m0, m1);
-        drop_pair(p.drop, ctr + 1, m2, m3);
-        pk = pack_bf16x4(make_float4(a.x * m0, a.y * m1, a.z * m2, a.w * m3));
+      if (p.drop.thresh != 0) {      // bf16(linear) -> dropout -> bf16, as autocast does; one counter = these 4 columns
+        uint32_t m01, m23;
+        drop_masks4(p.drop, static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N >> 2) + (c >> 2), m01, m23);
+        const float sc = p.drop.scale;
+        pk = pack_bf16x4(make_float4(a.x * sc, a.y * sc, a.z * sc, a.w * sc));
+        pk.x &= m01;
+        pk.y &= m23;
         a = unpack_bf16x4(pk);
       }
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) = pk;

@@ -421,11 +421,9 @@ gate_bwd_kernel(const float* __restrict__ dy, const void* __restrict__ f, int f_
       gacc += d.x * fv.x + d.y * fv.y + d.z * fv.z + d.w * fv.w;
       float4 t = make_float4(gate_t * d.x, gate_t * d.y, gate_t * d.z, gate_t * d.w);
       if (drop.thresh != 0) {     // backward of nn.Dropout after ff.2: the forward mask, re-created from (seed, element)
-        const uint32_t ctr = static_cast<uint32_t>(row) * static_cast<uint32_t>(D >> 1) + (c >> 1);
-        float m0, m1, m2, m3;
-        drop_pair(drop, ctr, m0, m1);
-        drop_pair(drop, ctr + 1, m2, m3);
-        t.x *= m0; t.y *= m1; t.z *= m2; t.w *= m3;
+        float m[4];
+        drop_mult4(drop, static_cast<uint32_t>(row) * static_cast<uint32_t>(D >> 2) + (c >> 2), m);
+        t.x *= m[0]; t.y *= m[1]; t.z *= m[2]; t.w *= m[3];
       }
       if (!out_is_f32) {
         t.x = __bfloat162float(__float2bfloat16_rn(t.x)); t.y = __bfloat162float(__float2bfloat16_rn(t.y));
@@ -721,11 +719,9 @@ __global__ void gate_res_f32_kernel(const float* __restrict__ x, float* __restri
   const float t = tanhf(__ldg(gate));
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
     float ov = o[i];
-    if (drop.thresh != 0) {      // same (row, column pair) counter as the bf16 FFN2 epilogue and gate_bwd_kernel
+    if (drop.thresh != 0) {      // same (row, 4-column) counter as the bf16 FFN2 epilogue and gate_bwd_kernel
       const uint32_t row = static_cast<uint32_t>(i / cols), c = static_cast<uint32_t>(i % cols);
-      float m0, m1;
-      drop_pair(drop, row * static_cast<uint32_t>(cols >> 1) + (c >> 1), m0, m1);
-      ov *= (c & 1) ? m1 : m0;
+      ov = drop_keep_scalar(drop, row * static_cast<uint32_t>((cols + 3) >> 2) + (c >> 2), int(c & 3)) ? ov * drop.scale : 0.f;
       o[i] = ov;
     }
     y[i] = x[i] + t * ov;

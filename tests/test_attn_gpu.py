@@ -149,6 +149,8 @@ def run_dropout(B, H, Lq, Lk, lengths, p, seed64, seed=0):
     (3, 2, 100, 201, [201, 77, 30], 0.25),         # odd Lk: pair counters restart per row
     (2, 4, 448, 750, [750, 333], 0.1),
     (2, 16, 448, 750, [750, 60], 0.1),             # config 3's heads and lengths
+    (2, 2, 128, 130, [130, 97], 0.01),             # threshold below the smallest normal fp16 pattern (packed compare, gxa_rng.cuh)
+    (2, 2, 128, 130, None, 0.9),
 ])
 def test_attention_dropout_matches_reference_with_same_mask(B, H, Lq, Lk, lengths, p):
     r = run_dropout(B, H, Lq, Lk, lengths, p, seed64=0x1234ABCD5678EF01)
