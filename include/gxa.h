@@ -145,6 +145,12 @@ int gxa_block_decode(const gxa_dims* d, const gxa_block_params* p, const void* w
 /* LayerNorm.forward (gate_cross_attention.py:8-10): fp32 statistics, eps 1e-5. out fp32 or bf16. */
 int gxa_layernorm_fwd(const float* x, const float* w, const float* b, void* out, int out_is_f32, float* mean,
                       float* rstd, int rows, int D, void* stream);
+/* pos_enc(ln(x)) in one pass (models/av_net.py:83-84, :88-89 with models/utils.py:21-28): out[r] = LN(x[r]) + pe[r % T];
+ * pe is the [T, D] fp32 head of the reference's positional table, rows = B * T.  Backward = gxa_layernorm_bwd. */
+int gxa_layernorm_pe_fwd(const float* x, const float* w, const float* b, const float* pe, int T, float* out, float* mean,
+                         float* rstd, int rows, int D, void* stream);
+/* out = a + b + c, fp32, n % 4 == 0: `fused + audio_features + video_features` (models/av_net.py:106) in one pass. */
+int gxa_sum3_f32(const float* a, const float* b, const float* c, float* out, size_t n, void* stream);
 /* dx = dres + LNbwd(g); dw += ..; db += ..  (g fp32) */
 int gxa_layernorm_bwd(const float* g, const float* x, const float* w, const float* mean, const float* rstd,
                       const float* dres, float* dx, float* dw, float* db, int rows, int D, void* stream);

@@ -56,6 +56,8 @@ SIGNATURES = {
     "gxa_block_decode_workspace_bytes": (_sz, [_dp]),
     "gxa_block_decode": (_i, [_dp, _bp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gxa_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _vp]),
+    "gxa_layernorm_pe_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _vp]),
+    "gxa_sum3_f32": (_i, [_vp, _vp, _vp, _vp, _sz, _vp]),
     "gxa_layernorm_bwd": (_i, [_vp] * 9 + [_i, _i, _vp]),
     "gxa_linear_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "gxa_linear_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),

@@ -14,9 +14,10 @@ The functions take the reference's OWN modules / buffers, so AVNet keeps its par
     video_features = proj_ln_pe(visual_out, self.video_proj, self.video_ln, self.pos_enc_video.pe)
     out = fuse_sum(fused, audio_features, video_features)
 
-GEMM (+bias) and LayerNorm run in the library (gxa_linear_*, gxa_layernorm_*: same kernels as the stack, tensor cores
-under autocast, split-bf16 fp32-accurate otherwise); the positional add and the 3-way sum are single torch elementwise
-passes (HBM-bound, no arithmetic to fuse them with yet -- folding ``+ pe`` into the LayerNorm store is listed as next).
+Everything runs in the library: GEMM (+bias) on the tcgen05 kernels (tensor cores under autocast, split-bf16
+fp32-accurate otherwise), LayerNorm with the positional add folded into its store (``gxa_layernorm_pe_fwd``: one HBM
+pass instead of two), and the 3-way sum as one pass (``gxa_sum3_f32``: 12 bytes read + 4 written per element instead
+of two binary adds' 24).  Achieved GB/s: tools/bench_glue.py, profiles/.
 """
 from __future__ import annotations
 
@@ -26,7 +27,7 @@ from typing import Optional
 import torch
 from torch import nn
 
-from .functional import LayerNormFn, LinearFn, resolve_precision
+from .functional import LayerNormFn, LinearFn, Sum3Fn, resolve_precision
 
 
 def positional_table(d_model: int, max_len: int = 5000, device=None) -> torch.Tensor:
@@ -51,10 +52,9 @@ def proj_ln_pe(x: torch.Tensor, proj: nn.Linear, ln: nn.Module, pe: torch.Tensor
                            "dimension 1")        # what the reference's broadcast add raises
     prec = resolve_precision(precision)
     h = LinearFn.apply(x, proj.weight, proj.bias, prec)
-    h = LayerNormFn.apply(h, ln.weight, ln.bias)
-    return h + pe[:, :T].to(h.dtype)
+    return LayerNormFn.apply(h, ln.weight, ln.bias, pe[0, :T] if pe.dim() == 3 else pe[:T])
 
 
 def fuse_sum(fused: torch.Tensor, audio_features: torch.Tensor, video_features: torch.Tensor) -> torch.Tensor:
     """``fused + audio_features + video_features`` (av_net.py:106)."""
-    return fused + audio_features + video_features
+    return Sum3Fn.apply(fused, audio_features, video_features)

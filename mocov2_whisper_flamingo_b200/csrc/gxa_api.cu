@@ -595,6 +595,17 @@ int gxa_layernorm_fwd(const float* x, const float* w, const float* b, void* out,
   GXA_TRY(ln_fwd(x, w, b, out, out_is_f32, mean, rstd, rows, D, reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
+int gxa_layernorm_pe_fwd(const float* x, const float* w, const float* b, const float* pe, int T, float* out, float* mean,
+                         float* rstd, int rows, int D, void* stream) {
+  if (!x || !w || !b || !pe || !out || T <= 0) return GXA_ERR_ARG;
+  GXA_TRY(ln_fwd(x, w, b, out, 1, mean, rstd, rows, D, reinterpret_cast<cudaStream_t>(stream), pe, T));
+  return 0;
+}
+int gxa_sum3_f32(const float* a, const float* b, const float* c, float* out, size_t n, void* stream) {
+  if (!a || !b || !c || !out) return GXA_ERR_ARG;
+  GXA_TRY(sum3_f32(a, b, c, out, n, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
 int gxa_layernorm_bwd(const float* g, const float* x, const float* w, const float* mean, const float* rstd,
                       const float* dres, float* dx, float* dw, float* db, int rows, int D, void* stream) {
   if (!g || !x || !w || !mean || !rstd || !dx || !dw || !db) return GXA_ERR_ARG;

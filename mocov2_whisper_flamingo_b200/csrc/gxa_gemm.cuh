@@ -172,59 +172,41 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
 // The TMEM load gives each thread one ROW of a 32x32 fp32 chunk.  The warp transposes it through a
 // 4 KB XOR-swizzled staging buffer so that 8 lanes cover one 128-byte row segment: every global
 // load/store of the fused epilogue is then fully coalesced, and bias / gate are loaded once per lane.
-// erf-GELU on packed f32x2 (FFMA2/FMUL2 on sm_100 halve the issue slots of the polynomial).
-//   Phi(u) = 0.5*erfc(-u/sqrt2);  Abramowitz-Stegun 7.1.26:  0.5*erfc(z) = hh(t)*exp(-z^2),  t = 1/(1 + p z),  z = |u|/sqrt2
-//   gelu(u)  = relu(u) - |u| * h(|u|)            h = hh(t) * exp(-u^2/2)   (|err| <= 1e-7 on Phi)
-//   gelu'(u) = 0.5 + copysign(0.5 - h, u) + u * phi0 * exp(-u^2/2)
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
+// erf-GELU on packed f32x2 (FFMA2/FMUL2 on sm_100 halve the issue slots of the polynomials): gelu_both2 below.
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 __device__ __forceinline__ float2 f2(float a) { return make_float2(a, a); }
-// returns -h(|u|) and e = exp(-u^2/2)
-__device__ __forceinline__ float2 gelu_neg_h2(float2 u, float2 au, float2& e) {
-  const float2 d = __ffma2_rn(au, f2(0.3275911f * 0.70710678118654752f), f2(1.0f));
-  const float2 t = make_float2(rcp_approx(d.x), rcp_approx(d.y));
-  const float2 w = __fmul2_rn(__fmul2_rn(u, f2(-0.5f * 1.4426950408889634f)), u);
-  e = make_float2(ex2_approx(w.x), ex2_approx(w.y));
-  float2 poly = __ffma2_rn(t, f2(-0.5f * 1.061405429f), f2(0.5f * 1.453152027f));
-  poly = __ffma2_rn(t, poly, f2(-0.5f * 1.421413741f));
-  poly = __ffma2_rn(t, poly, f2(0.5f * 0.284496736f));
-  poly = __ffma2_rn(t, poly, f2(-0.5f * 0.254829592f));
-  return __fmul2_rn(__fmul2_rn(poly, t), e);
-}
-__device__ __forceinline__ float2 gelu_fast2(float2 u) {
-  const float2 au = make_float2(fabsf(u.x), fabsf(u.y));
-  float2 e;
-  const float2 nh = gelu_neg_h2(u, au, e);
-  return __ffma2_rn(au, nh, make_float2(fmaxf(u.x, 0.f), fmaxf(u.y, 0.f)));
-}
-__device__ __forceinline__ float2 gelu_grad_fast2(float2 u) {
-  const float2 au = make_float2(fabsf(u.x), fabsf(u.y));
-  float2 e;
-  const float2 nh = gelu_neg_h2(u, au, e);
-  const float2 q = __fadd2_rn(nh, f2(0.5f));                        // 0.5 - h >= 0
-  const float2 cdf = __fadd2_rn(make_float2(copysignf(q.x, u.x), copysignf(q.y, u.y)), f2(0.5f));
-  return __ffma2_rn(__fmul2_rn(u, f2(0.3989422804014327f)), e, cdf);
-}
-// value and derivative from one exponential / reciprocal / polynomial
+// value and derivative from ONE exponential and no reciprocal (round 2).  The Abramowitz-Stegun 7.1.26 form used in round 1 costs two MUFU
+// operations per element (rcp + ex2): at 16 / clk / SM that is 4096 cycles for a CTA's 128 x 256 tile -- as long as the
+// tile's main loop at K = 1024, so the FFN1 epilogue could not hide under it (1113 vs 1450 TFLOP/s for the plain-bf16
+// epilogue).  Here   1 - Phi(a) = 0.5 * exp(-q(a)),  q = c1 a + ... + c5 a^5,  a = |u|   (minimax fit on [0, 8], q keeps
+// growing beyond; max |gelu error| 1.8e-6, max |gelu' error| 1.8e-6 against erf in float64 -- three orders of magnitude
+// below the bf16 rounding of the two outputs), and the density comes from the same exponential:
+//   phi(a) ~= d/da Phi = h * q'(a),  h = 1 - Phi(a)
+//   gelu(u)  = relu(u) - a h            gelu'(u) = 0.5 + copysign(0.5 - h + a h q'(a), u)
 __device__ __forceinline__ void gelu_both2(float2 u, float2& g, float2& dg) {
-  const float2 au = make_float2(fabsf(u.x), fabsf(u.y));
-  float2 e;
-  const float2 nh = gelu_neg_h2(u, au, e);
-  g = __ffma2_rn(au, nh, make_float2(fmaxf(u.x, 0.f), fmaxf(u.y, 0.f)));
-  const float2 q = __fadd2_rn(nh, f2(0.5f));
-  const float2 cdf = __fadd2_rn(make_float2(copysignf(q.x, u.x), copysignf(q.y, u.y)), f2(0.5f));
-  dg = __ffma2_rn(__fmul2_rn(u, f2(0.3989422804014327f)), e, cdf);
+  constexpr float L2E = 1.4426950408889634f;
+  constexpr float c1 = 0.7978507334384695f, c2 = 0.3183989204813974f, c3 = 0.036381011328425965f,
+                  c4 = -0.005117729294495289f, c5 = 0.00036235314137177013f;
+  const float2 a = make_float2(fabsf(u.x), fabsf(u.y));
+  float2 q = __ffma2_rn(a, f2(-c5 * L2E), f2(-c4 * L2E));          // -q(a) * log2(e) - 1  (the 0.5 rides in the exponent)
+  q = __ffma2_rn(a, q, f2(-c3 * L2E));
+  q = __ffma2_rn(a, q, f2(-c2 * L2E));
+  q = __ffma2_rn(a, q, f2(-c1 * L2E));
+  q = __ffma2_rn(a, q, f2(-1.0f));
+  float2 dq = __ffma2_rn(a, f2(5.f * c5), f2(4.f * c4));           // q'(a)
+  dq = __ffma2_rn(a, dq, f2(3.f * c3));
+  dq = __ffma2_rn(a, dq, f2(2.f * c2));
+  dq = __ffma2_rn(a, dq, f2(c1));
+  const float2 h = make_float2(ex2_approx(q.x), ex2_approx(q.y));
+  const float2 ah = __fmul2_rn(a, h);
+  g = __fadd2_rn(make_float2(fmaxf(u.x, 0.f), fmaxf(u.y, 0.f)), make_float2(-ah.x, -ah.y));
+  const float2 r = __ffma2_rn(ah, dq, __fadd2_rn(f2(0.5f), make_float2(-h.x, -h.y)));     // 0.5 - h + a h q'
+  dg = __fadd2_rn(make_float2(copysignf(r.x, u.x), copysignf(r.y, u.y)), f2(0.5f));
 }
-__device__ __forceinline__ float gelu_fast(float u) { return gelu_fast2(make_float2(u, u)).x; }
-__device__ __forceinline__ float gelu_grad_fast(float u) { return gelu_grad_fast2(make_float2(u, u)).x; }
 __device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
   uint2 r;
   r.x = pack_bf16(v.x, v.y);

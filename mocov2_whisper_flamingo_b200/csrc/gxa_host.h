@@ -73,7 +73,8 @@ int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1
 
 // ---- row-wise / elementwise kernels (gxa_rowwise.cu)
 int ln_fwd(const float* x, const float* w, const float* b, void* out, int out_is_f32, float* mean, float* rstd, int rows,
-           int D, cudaStream_t s);
+           int D, cudaStream_t s, const float* add = nullptr, int add_period = 0);   // optional fused + add[row % period]
+int sum3_f32(const float* a, const float* b, const float* c, float* out, size_t n, cudaStream_t s);
 // dx = dres + LNbwd(g; x, w);  dw += sum g*xhat;  db += sum g;  optional gated output:
 //   dgate_accum += sum(dx * o),  dout(bf16 or f32) = tanh(gate) * dx,  dbias_out += colsum(dout)
 int ln_bwd(const void* g, int g_is_f32, const float* x, const float* w, const float* mean, const float* rstd,

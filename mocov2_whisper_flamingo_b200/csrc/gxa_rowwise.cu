@@ -42,13 +42,17 @@ template <int NV>   // D = 128 * NV
 __global__ void __launch_bounds__(RW_WARPS * 32) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                                const float* __restrict__ b, void* __restrict__ out,
                                                                int out_is_f32, float* __restrict__ mean,
-                                                               float* __restrict__ rstd, int rows) {
+                                                               float* __restrict__ rstd, int rows,
+                                                               const float* __restrict__ add, int add_period) {
   pdl_launch_dependents();
   pdl_wait();
   constexpr int D = 128 * NV;
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * RW_WARPS + (threadIdx.x >> 5);
   if (row >= rows) return;
+  // optional fused broadcast add after the affine (the positional table of models/utils.py:21-28: row t of `add` goes to
+  // every row with row % add_period == t), so `pos_enc(ln(.))` is one pass over the tensor
+  const float* ar = add ? add + size_t(row % add_period) * D : nullptr;
   const float* xr = x + size_t(row) * D;
   float4 v[NV];
   float s = 0.f;
@@ -77,6 +81,10 @@ __global__ void __launch_bounds__(RW_WARPS * 32) ln_fwd_kernel(const float* __re
     o.y = (v[i].y - mu) * rs * g.y + be.y;
     o.z = (v[i].z - mu) * rs * g.z + be.z;
     o.w = (v[i].w - mu) * rs * g.w + be.w;
+    if (ar) {
+      const float4 a4 = ld4(ar + c);
+      o.x += a4.x; o.y += a4.y; o.z += a4.z; o.w += a4.w;
+    }
     st4_any(out, size_t(row) * D + c, out_is_f32, o);
   }
 }
@@ -97,11 +105,30 @@ __global__ void __launch_bounds__(RW_WARPS * 32) ln_fwd_kernel(const float* __re
 static inline int check_launch() { count_launch(); return cudaGetLastError() == cudaSuccess ? 0 : GXA_ERR_CUDA; }
 
 int ln_fwd(const float* x, const float* w, const float* b, void* out, int out_is_f32, float* mean, float* rstd, int rows,
-           int D, cudaStream_t s) {
+           int D, cudaStream_t s, const float* add, int add_period) {
   if (D % 128) return GXA_ERR_SHAPE;
   if (rows == 0) return 0;
+  if (add != nullptr && add_period <= 0) return GXA_ERR_ARG;
   const int grid = (rows + RW_WARPS - 1) / RW_WARPS;
-  GXA_NV_DISPATCH(D, (launch_pdl(ln_fwd_kernel<NV>, dim3(grid), dim3(RW_WARPS * 32), 0, s, x, w, b, out, out_is_f32, mean, rstd, rows)));
+  GXA_NV_DISPATCH(D, (launch_pdl(ln_fwd_kernel<NV>, dim3(grid), dim3(RW_WARPS * 32), 0, s, x, w, b, out, out_is_f32, mean, rstd, rows,
+                                 add, add_period)));
+  return check_launch();
+}
+
+// out = a + b + c  (fp32, n % 4 == 0): the post-fusion sum of models/av_net.py:106 in one pass
+__global__ void sum3_f32_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ c,
+                                float* __restrict__ out, size_t n4) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+    const float4 x = ld4(a + 4 * i), y = ld4(b + 4 * i), z = ld4(c + 4 * i);
+    *reinterpret_cast<float4*>(out + 4 * i) = make_float4(x.x + y.x + z.x, x.y + y.y + z.y, x.z + y.z + z.z, x.w + y.w + z.w);
+  }
+}
+int sum3_f32(const float* a, const float* b, const float* c, float* out, size_t n, cudaStream_t s) {
+  if (n % 4) return GXA_ERR_SHAPE;
+  if (!n) return 0;
+  size_t blocks = (n / 4 + 255) / 256;
+  const size_t cap = size_t(num_sms()) * 8;
+  sum3_f32_kernel<<<unsigned(blocks < cap ? blocks : cap), 256, 0, s>>>(a, b, c, out, n / 4);
   return check_launch();
 }
 

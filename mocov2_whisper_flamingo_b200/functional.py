@@ -266,7 +266,9 @@ class LayerNormFn(torch.autograd.Function):
     """LayerNorm.forward (reference: models/gate_cross_attention.py:8-10): fp32 statistics, output in x.dtype."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias):
+    def forward(ctx, x, weight, bias, pe=None):
+        """pe: optional [T, D] fp32 table added after the affine (out[b, t] = LN(x[b, t]) + pe[t]); the result is then
+        fp32 like the reference's ``ln(x) + pe`` (fp32 buffer, models/utils.py:9)."""
         L = _lib.lib()
         _require_cuda(x, "x")
         D = x.shape[-1]
@@ -276,11 +278,20 @@ class LayerNormFn(torch.autograd.Function):
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)
         rstd = torch.empty_like(mean)
         w, b = _f32c(weight), _f32c(bias)
-        check(L.gxa_layernorm_fwd(xf.data_ptr(), w.data_ptr(), b.data_ptr(), out.data_ptr(), 1, mean.data_ptr(),
-                                  rstd.data_ptr(), rows, D, _stream()), "gxa_layernorm_fwd")
+        if pe is None:
+            check(L.gxa_layernorm_fwd(xf.data_ptr(), w.data_ptr(), b.data_ptr(), out.data_ptr(), 1, mean.data_ptr(),
+                                      rstd.data_ptr(), rows, D, _stream()), "gxa_layernorm_fwd")
+        else:
+            T = x.shape[-2]
+            pef = _f32c(pe).view(-1, D)
+            if pef.shape[0] != T or pef.device != x.device:
+                raise RuntimeError(f"gxa_b200: positional table {tuple(pe.shape)} does not match [T={T}, D={D}] on {x.device}")
+            check(L.gxa_layernorm_pe_fwd(xf.data_ptr(), w.data_ptr(), b.data_ptr(), pef.data_ptr(), T, out.data_ptr(),
+                                         mean.data_ptr(), rstd.data_ptr(), rows, D, _stream()), "gxa_layernorm_pe_fwd")
         ctx.save_for_backward(xf, w, mean, rstd)
         ctx.shape, ctx.dtype = x.shape, x.dtype
-        return out.view(x.shape).to(x.dtype)
+        ctx.has_pe = pe is not None
+        return out.view(x.shape) if pe is not None else out.view(x.shape).to(x.dtype)
 
     @staticmethod
     def backward(ctx, g):
@@ -293,7 +304,31 @@ class LayerNormFn(torch.autograd.Function):
         db = torch.zeros_like(dw)
         check(L.gxa_layernorm_bwd(gf.data_ptr(), xf.data_ptr(), w.data_ptr(), mean.data_ptr(), rstd.data_ptr(), None,
                                   dx.data_ptr(), dw.data_ptr(), db.data_ptr(), rows, D, _stream()), "gxa_layernorm_bwd")
-        return dx.view(ctx.shape).to(ctx.dtype), dw, db
+        return (dx.view(ctx.shape).to(ctx.dtype), dw, db) + ((None,) if ctx.has_pe else ())
+
+
+class Sum3Fn(torch.autograd.Function):
+    """``a + b + c`` in one pass (reference: models/av_net.py:106 ``fused + audio_features + video_features``)."""
+
+    @staticmethod
+    def forward(ctx, a, b, c):
+        L = _lib.lib()
+        for t, n in ((a, "fused"), (b, "audio_features"), (c, "video_features")):
+            _require_cuda(t, n)
+        if not (a.shape == b.shape == c.shape):
+            raise RuntimeError(f"gxa_b200: fuse_sum shapes differ: {tuple(a.shape)}, {tuple(b.shape)}, {tuple(c.shape)}")
+        af, bf, cf = _f32c(a), _f32c(b), _f32c(c)
+        out = torch.empty_like(af)
+        n = af.numel()
+        if n % 4:
+            raise RuntimeError("gxa_b200: fuse_sum needs a multiple of 4 elements")
+        check(L.gxa_sum3_f32(af.data_ptr(), bf.data_ptr(), cf.data_ptr(), out.data_ptr(), n, _stream()), "gxa_sum3_f32")
+        ctx.dtypes = (a.dtype, b.dtype, c.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return tuple(g.to(dt) for dt in ctx.dtypes)
 
 
 class LinearFn(torch.autograd.Function):
