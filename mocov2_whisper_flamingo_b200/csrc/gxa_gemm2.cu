@@ -25,7 +25,7 @@ constexpr int G2_STAGE_BYTES = G2_A_BYTES + G2_B_BYTES;
 //
 // STG = 0 is the configuration above.  A non-zero STG overrides the ring depth: a shallower ring leaves shared memory on
 // the SM for a co-resident CTA of an HBM-bound row-wise kernel -- experiment switch
-// GXA_WGRAD_STAGES for the fp32-accumulating (weight-gradient / dxa) GEMMs, off by default.
+// GXA_WGRAD_STAGES for the fp32-accumulating (weight-gradient / dxa) GEMMs (default 5, see launch2_layout).
 template <int EPI, int STG = 0>
 struct G2Cfg {
   static constexpr int EPI_WARPS = (EPI == EPI_BIAS_GELU || EPI == EPI_GELU_BWD) ? 16 : 8;
@@ -269,7 +269,10 @@ static int launch2_f32_shallow(const GemmOp& op, const GemmParams& p, cudaStream
 template <int EPI>
 static int launch2_layout(const GemmOp& op, const GemmParams& p, cudaStream_t s) {
   if constexpr (EPI == EPI_F32) {
-    static const int shallow = [] { const char* e = getenv("GXA_WGRAD_STAGES"); return e ? atoi(e) : 0; }();
+    // default 5 (round 2, c3 step on one B200: 6 stages 86.9 ms, 5 stages 85.8 ms, 4 stages 86.5 ms): the shallower ring
+    // leaves 32 KB of shared memory per SM, enough for a CTA of the HBM-bound row-wise kernels to run beside the
+    // weight-gradient GEMM of the other stream instead of behind it.  GXA_WGRAD_STAGES=6 restores the deep ring.
+    static const int shallow = [] { const char* e = getenv("GXA_WGRAD_STAGES"); return e ? atoi(e) : 5; }();
     if (shallow == 4) return launch2_f32_shallow<4>(op, p, s);
     if (shallow == 5) return launch2_f32_shallow<5>(op, p, s);
   }

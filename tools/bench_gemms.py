@@ -12,6 +12,8 @@ from mocov2_whisper_flamingo_b200 import _lib  # noqa: E402
 from gpu_util import ptr, stream  # noqa: E402
 
 L = _lib.lib()
+if os.environ.get("SM_LIMIT"):        # experiment: persistent grids sized for fewer SMs (is a GEMM chip-bound or SM-bound?)
+    _lib.set_sm_limit(int(os.environ["SM_LIMIT"]))
 B, Lq, Lk, D = int(os.environ.get("BB", 64)), 448, 750, int(os.environ.get("DD", 1024))
 M, Mk = B * Lq, B * Lk
 E = _lib
