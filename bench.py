@@ -28,6 +28,9 @@ import json
 import os
 
 os.environ.setdefault("NCCL_MAX_CTAS", "8")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
+# stdout carries exactly ONE JSON line: NCCL's own banner ("NCCL version ...", printed at NCCL_DEBUG=VERSION) goes to stderr
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"
 import statistics
 import subprocess
 import sys
@@ -475,7 +478,7 @@ def run_product(args, D, H, layers, GB, Lq, Lk, variable):
         torch.cuda.synchronize()
         full = {n: (p.grad / world).clone() for n, p in model.named_parameters()}
         model.grad_hook = hook
-        worst = 0.0
+        worst, worst_name, gate_err, gate_ref = 0.0, "", 0.0, 0.0
         for accumulate in (False, True):
             model.zero_grad(set_to_none=True)
             parts = [idx] if not accumulate else [idx[: (B + 1) // 2], idx[(B + 1) // 2:]]
@@ -489,17 +492,27 @@ def run_product(args, D, H, layers, GB, Lq, Lk, variable):
             torch.cuda.synchronize()
             for n, p in model.named_parameters():
                 ref, got = full[n], p.grad
+                if n.endswith("_gate"):
+                    # a gate gradient is ONE scalar, the sum of B*Lq*D signed terms that may cancel far below their natural
+                    # size: the 2 * layers gate gradients are compared as one vector (max |diff| / max |ref| over all gates)
+                    gate_err = max(gate_err, float((got - ref).abs().max()))
+                    gate_ref = max(gate_ref, float(ref.abs().max()))
+                    continue
                 den = float(ref.abs().max())
                 if n.endswith("in_proj_bias"):                      # the bk third is rounding noise around 0
                     ref, got = torch.cat([ref[:D], ref[2 * D:]]), torch.cat([got[:D], got[2 * D:]])
                 if den > 0:
-                    worst = max(worst, float((got - ref).abs().max()) / den)
-        wt = torch.tensor([worst], device="cuda")
+                    e = float((got - ref).abs().max()) / den
+                    if e > worst:
+                        worst, worst_name = e, n + (" (accumulate)" if accumulate else "")
+        wt = torch.tensor([worst, gate_err / gate_ref if gate_ref > 0 else 0.0], device="cuda")
         dist.all_reduce(wt, op=dist.ReduceOp.MAX)
-        dp_check = {"max_rel_err": float(wt[0]), "tolerance": 5e-3, "ok": bool(float(wt[0]) < 5e-3),
+        dp_check = {"max_rel_err": float(wt[0]), "worst_param_rank0": worst_name, "gates_vector_rel_err": float(wt[1]),
+                    "tolerance": 2e-2, "ok": bool(float(wt[0]) < 2e-2 and float(wt[1]) < 2e-2),
                     "what": "AVG-all-reduced shard gradients (plain step, and 2 micro-batches with no_sync) vs full-batch gradient / N "
-                            "on every rank, all parameters, dropout off, bf16 mode (differences: fp32 summation order and the bf16 "
-                            "roundings it flips)"}
+                            "on every rank, every parameter tensor by max-norm, the scalar gate gradients as one vector; dropout off, "
+                            "bf16 mode (differences: fp32 summation order and the bf16 roundings it flips through 24 layers; "
+                            "tolerance = the bf16 budget of north_star)"}
         model.zero_grad(set_to_none=True)
         del a_g, v_g, dy_g, full
         model.train()
