@@ -86,6 +86,9 @@ long long gxa_launch_count(void);
  * the budget so that no CTA of a statically partitioned grid has to wait for a second wave.  n_sms <= 0 restores the
  * whole device; returns the previous limit. */
 int gxa_set_sm_limit(int n_sms);
+/* The one collective of the path (the reference's DDP gradient all-reduce, train.py:319) is host-side by design:
+ * mocov2_whisper_flamingo_b200/parallel.py drives NCCL through torch.distributed on a communication stream, one flat
+ * fp32 bucket per layer.  There is no gxa_allreduce_layer entry point: the library never owns a communicator. */
 
 /* Host-side evaluation of the training-mode dropout masks (reference: nn.MultiheadAttention(dropout=p) on the attention
  * probabilities and nn.Dropout(p) after ff.2, models/gate_cross_attention.py:16, :26).  The kernels never store a mask:
