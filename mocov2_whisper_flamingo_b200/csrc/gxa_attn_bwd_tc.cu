@@ -261,33 +261,41 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
     const uint32_t p_row = smem_u32(sm.p) + (cq >> 1) * TILE + r * 128;
     const uint32_t s_row = smem_u32(sm.ds) + (cq >> 1) * TILE + r * 128;
-    auto row_stats = [&](const Item& it, int i, float& ls, float& de) {
+    // the compute warps keep only (b*H + h, first key) of an item: every register that stays live across their loop is
+    // one they cannot use in it (80-register cap; ncu r02: 13 % of their stall samples were waits on re-loads of spilled
+    // item fields at the top of each iteration)
+    auto decode_c = [&](int w, int& bh, int& k0) -> bool {
+      bh = w / nkb;
+      k0 = (w - bh * nkb) * BK;
+      return sm.live[(w - blockIdx.x) / gridDim.x] != 0;
+    };
+    auto row_stats = [&](int bh, int i, float& ls, float& de) {
       const int row = i * BQ + r;
       ls = INFINITY;            // rows past Lq: P = exp2(-inf) = 0 (ls is pre-multiplied by log2 e below)
       de = 0.f;
       if (row < Lq) {
-        const size_t o = (size_t(it.b) * H + it.h) * Lq + row;
+        const size_t o = size_t(bh) * Lq + row;
         // asm volatile: keeps the loads HERE (one iteration ahead of their use); plain __ldg was sunk to the use
         asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(ls) : "l"(lse + o));
         asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(de) : "l"(delta + o));
       }
     };
     int w = blockIdx.x, n = 0, g = 0;
-    Item cur, nxt;
-    while (w < total && !decode(w, cur)) w += gridDim.x;
+    int cur_bh = 0, cur_k0 = 0, nxt_bh = 0, nxt_k0 = 0;
+    while (w < total && !decode_c(w, cur_bh, cur_k0)) w += gridDim.x;
     float ls = 0.f, de = 0.f, ls_n, de_n;
-    if (w < total) row_stats(cur, 0, ls, de);
+    if (w < total) row_stats(cur_bh, 0, ls, de);
     while (w < total) {
       int w2 = w + gridDim.x;
-      while (w2 < total && !decode(w2, nxt)) w2 += gridDim.x;
+      while (w2 < total && !decode_c(w2, nxt_bh, nxt_k0)) w2 += gridDim.x;
       mbar_wait(&sm.kb_full[n & 1], (n >> 1) & 1);
       const float* kbias = sm.kbias[n & 1] + cq * 32;
       const bool any_masked = (sm.kb_any[n & 1][0] | sm.kb_any[n & 1][1] | sm.kb_any[n & 1][2] | sm.kb_any[n & 1][3]) != 0;
       for (int i = 0; i < nq; ++i, ++g) {
         if (warp == 0) STAMP(1, 5);
         ls_n = 0.f; de_n = 0.f;
-        if (i + 1 < nq) row_stats(cur, i + 1, ls_n, de_n);       // one iteration ahead: latency hidden by the math
-        else if (w2 < total) row_stats(nxt, 0, ls_n, de_n);
+        if (i + 1 < nq) row_stats(cur_bh, i + 1, ls_n, de_n);       // one iteration ahead: latency hidden by the math
+        else if (w2 < total) row_stats(nxt_bh, 0, ls_n, de_n);
         if (warp == 0) STAMP(1, 0);
         mbar_wait(&sm.sdp_full, g & 1);
         if (warp == 0) STAMP(1, 1);
@@ -317,8 +325,8 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
           uint32_t ctr = 0;               // same function of (row, key) as the forward (gxa_rng.cuh): 4 keys per counter
           if (drop.thresh != 0)
-            ctr = (static_cast<uint32_t>(cur.b * H + cur.h) * Lq + (i * BQ + r)) * static_cast<uint32_t>((Lk + 3) >> 2) +
-                  ((cur.k0 + cq * 32 + hf * 16) >> 2);
+            ctr = (static_cast<uint32_t>(cur_bh) * Lq + (i * BQ + r)) * static_cast<uint32_t>((Lk + 3) >> 2) +
+                  ((cur_k0 + cq * 32 + hf * 16) >> 2);
 #pragma unroll
           for (int w = 0; w < 4; ++w) {   // one counter = 4 keys = 2 packed pairs
             uint32_t mk[2] = {0xffffffffu, 0xffffffffu};
@@ -373,7 +381,8 @@ attn_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
       ++n;
       w = w2;
-      cur = nxt;
+      cur_bh = nxt_bh;
+      cur_k0 = nxt_k0;
     }
   } else {
     // ------------------------------------------------------------ drain warps: dQ every iteration; dK/dV and the
