@@ -27,7 +27,7 @@ import contextlib
 import json
 import os
 
-os.environ.setdefault("NCCL_MAX_CTAS", "8")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
+os.environ.setdefault("NCCL_MAX_CTAS", "16")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
 # stdout carries exactly ONE JSON line: NCCL's own banner ("NCCL version ...", printed at NCCL_DEBUG=VERSION) goes to stderr
 if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
     os.environ["NCCL_DEBUG"] = "WARN"

@@ -250,7 +250,7 @@ class BlockFn(torch.autograd.Function):
         if shared.grad_hook is not None:
             # data-parallel hook (parallel.py): installs the layer's gradients as p.grad itself and orders the all-reduce;
             # autograd must then not see them (AccumulateGrad would touch the bucket while NCCL reduces it in place)
-            owned = bool(shared.grad_hook(ctx.token, bucket))
+            owned = bool(shared.grad_hook(ctx.token, bucket, views))
         dxa = None
         if dims.has_xa and shared.dxa_wanted and ctx.token is shared.first_token:
             dxa = shared.dxa          # every layer has accumulated into it by now

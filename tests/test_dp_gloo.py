@@ -86,9 +86,10 @@ def _worker(rank: int, world: int, port: int, average: bool):
             views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
             for v, key in zip(views, LAYER_KEYS):
                 v.copy_(local[f"layers.{i}.{key}"])
-            assert model.grad_hook(model.layers[i], bucket) is True      # the hook installs p.grad itself
+            # no gradient present: the hook leaves the views to autograd (which only stores them) ...
+            assert model.grad_hook(model.layers[i], bucket, views) is False
             for v, prm in zip(views, model.layers[i]._params()):
-                assert prm.grad is not None and prm.grad.data_ptr() == v.data_ptr()
+                prm.grad = v                                                  # ... as AccumulateGrad does
         for n, prm in model.named_parameters():
             if not n.startswith("layers."):
                 prm.grad = local[n].clone()
@@ -125,7 +126,12 @@ def _worker(rank: int, world: int, port: int, average: bool):
                     views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
                     for v, key in zip(views, LAYER_KEYS):
                         v.copy_(loc[f"layers.{i}.{key}"])
-                    model.grad_hook(model.layers[i], bucket)
+                    had = [prm.grad is not None for prm in model.layers[i]._params()]
+                    owned = model.grad_hook(model.layers[i], bucket, views)
+                    assert owned is any(had)          # gradients present: the hook owns them; none: autograd adopts the views
+                    if not owned:
+                        for v, prm in zip(views, model.layers[i]._params()):
+                            prm.grad = v
                 for n, prm in model.named_parameters():
                     if not n.startswith("layers."):
                         prm.grad = loc[n].clone() if prm.grad is None else prm.grad + loc[n]

@@ -46,6 +46,16 @@ def step():
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+# host time to ENQUEUE one step (no synchronisation inside): if it approaches the device time the step is launch-bound
+import time  # noqa: E402
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for _ in range(3):
+    step()
+t_host = (time.perf_counter() - t0) / 3
+torch.cuda.synchronize()
+t_dev = (time.perf_counter() - t0) / 3
+print(f"{wl} B={B}: host enqueue {t_host * 1e3:.2f} ms/step, wall {t_dev * 1e3:.2f} ms/step (3 steps back to back)")
 if os.environ.get("PLAIN"):
     print("plain run done")
     sys.exit(0)
