@@ -42,7 +42,7 @@ from .functional import PARAM_SHAPES, bucket_layout
 
 class DataParallelGrads:
     def __init__(self, fusion, process_group: Optional[dist.ProcessGroup] = None, average: bool = True,
-                 comm_sms: Optional[int] = None):
+                 comm_sms: Optional[int] = None, grad_dtype: Optional[torch.dtype] = None):
         self.fusion = fusion
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
@@ -56,6 +56,15 @@ class DataParallelGrads:
             comm_sms = int(os.environ.get("GXA_DP_COMM_SMS", os.environ.get("NCCL_MAX_CTAS", "16")))
         self.comm_sms = max(0, comm_sms)
         self._limited = False
+        # Optional compressed exchange (as torch DDP's bf16_compress_hook): the layer buckets travel as bf16 and come back
+        # into the fp32 bucket.  Halves the NVLink bytes and the time NCCL's CTAs hold their SMs; costs one rounding to
+        # 8 mantissa bits per rank's contribution (the sum itself is carried out by NCCL in bf16).  Default: fp32, the
+        # reference's DDP behaviour (train.py:319).
+        if grad_dtype is None and os.environ.get("GXA_DP_GRAD_DTYPE", "") in ("bf16", "bfloat16"):
+            grad_dtype = torch.bfloat16
+        if grad_dtype not in (None, torch.float32, torch.bfloat16):
+            raise ValueError("grad_dtype must be None, torch.float32 or torch.bfloat16")
+        self.grad_dtype = None if grad_dtype == torch.float32 else grad_dtype
         # diagnostics only (tools/, never bench.py's reported line): time the step without the collective
         self._diag_skip = os.environ.get("GXA_DP_DIAG_NO_ALLREDUCE") == "1"
         fusion.grad_hook = self._on_layer_grads
@@ -101,7 +110,12 @@ class DataParallelGrads:
         if self.comm_stream is None:           # CPU/gloo (tests): synchronous
             if self.average:
                 target.div_(self.world)
-            dist.all_reduce(target, group=self.pg)
+            if self.grad_dtype is not None:
+                wire = target.to(self.grad_dtype)
+                dist.all_reduce(wire, group=self.pg)
+                target.copy_(wire)
+            else:
+                dist.all_reduce(target, group=self.pg)
             return owned
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream())
@@ -114,7 +128,12 @@ class DataParallelGrads:
             self.comm_stream.wait_event(ready)
             # NCCL averages inside the collective: no separate pass over the bucket on the communication stream
             op = dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM
-            self.pending.append(dist.all_reduce(target, op=op, group=self.pg, async_op=True))
+            if self.grad_dtype is not None:
+                wire = target.to(self.grad_dtype)                  # both casts run on the communication stream
+                dist.all_reduce(wire, op=op, group=self.pg, async_op=True).wait()
+                target.copy_(wire)
+            else:
+                self.pending.append(dist.all_reduce(target, op=op, group=self.pg, async_op=True))
         target.record_stream(self.comm_stream)
         self._touched.append(target)
         return owned

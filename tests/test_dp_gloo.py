@@ -53,7 +53,7 @@ def _port_grads(state, audio, video, mask, dy):
     return {k: v.grad for k, v in p.items()}
 
 
-def _worker(rank: int, world: int, port: int, average: bool):
+def _worker(rank: int, world: int, port: int, average: bool, wire: str = "fp32"):
     import mocov2_whisper_flamingo_b200 as G
     from mocov2_whisper_flamingo_b200.functional import PARAM_SHAPES, bucket_layout
     from mocov2_whisper_flamingo_b200.parallel import DataParallelGrads, balanced_shards, shard_batch
@@ -67,7 +67,10 @@ def _worker(rank: int, world: int, port: int, average: bool):
                     p.fill_(0.5 + 0.1 * rank)
                 elif n.endswith("bias"):
                     p.uniform_(-0.1, 0.1)
-        ddp = DataParallelGrads(model, average=average)
+        # wire = "bf16": the layer buckets travel as bf16 (torch DDP's bf16_compress_hook equivalent); each contribution is
+        # rounded to 8 mantissa bits once and the sum is formed in bf16 -> 2^-8 relative per element at world 2
+        ddp = DataParallelGrads(model, average=average, grad_dtype=torch.bfloat16 if wire == "bf16" else None)
+        tol = 2e-5 if wire == "fp32" else 8e-3
         ddp.broadcast_parameters(src=0)                     # ... and are made identical to rank 0's
         state = {k: v.detach().clone() for k, v in model.state_dict().items()}
         flat = torch.cat([v.reshape(-1) for v in state.values()])
@@ -101,7 +104,7 @@ def _worker(rank: int, world: int, port: int, average: bool):
             ref = full[n] * scale
             den = float(ref.abs().max())
             err = float((prm.grad - ref).abs().max()) / (den if den > 0 else 1.0)
-            assert err < 2e-5, (n, err)
+            assert err < (tol if n.startswith("layers.") else 2e-5), (n, err)
 
         # ---- gradient accumulation (reference: accumulate_grad_batches, config.py:42): two micro-batches, the first one
         # inside no_sync(); p.grad is already present in the second backward, so the new bucket has to be ADDED to the
@@ -143,7 +146,7 @@ def _worker(rank: int, world: int, port: int, average: bool):
                 ref = ref + 0.25 * (1.0 if average else world)
             den = float(ref.abs().max())
             err = float((prm.grad - ref).abs().max()) / (den if den > 0 else 1.0)
-            assert err < 2e-5, ("accumulate", n, err)
+            assert err < (tol if n.startswith("layers.") else 2e-5), ("accumulate", n, err)
 
         # sharding helpers: every rank derives the same partition from the same lengths
         lengths = [750, 60, 400, 399, 90, 700, 61, 333]
@@ -163,3 +166,7 @@ def _worker(rank: int, world: int, port: int, average: bool):
 def test_world_size_2_gradient_allreduce_matches_full_batch(average):
     world = 2
     mp.spawn(_worker, args=(world, _free_port(), average), nprocs=world, join=True)
+
+
+def test_world_size_2_bf16_gradient_exchange():
+    mp.spawn(_worker, args=(2, _free_port(), True, "bf16"), nprocs=2, join=True)
