@@ -162,6 +162,21 @@ int gxa_layernorm_bwd(const float* g, const float* x, const float* w, const floa
 size_t gxa_linear_workspace_bytes(int rows, int in_f, int out_f, int precision);
 int gxa_linear_fwd(const float* x, const float* w, const float* b, float* y, int rows, int in_f, int out_f,
                    int precision, void* workspace, void* stream);
+/* gxa_linear_fwd (bf16 contraction) with NO caller workspace and NO allocation of any kind (no cudaMalloc / cudaFree, no
+ * allocating library call).  This entry point has no counterpart in the reference: it was added
+ * for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The bf16 operand copies live in a file-scope `static __device__` array inside the library
+ * (csrc/gxa_noalloc.cu) of GXA_LINEAR_FWD_STATIC_MAX_BYTES = 8 MiB, which every GPU that uses the entry point holds
+ * until the process exits (the first call on a device is the set-up: symbol-address lookup, and -- under CUDA's lazy
+ * module loading -- the point where the driver materialises the array; make one warm call before a capture / timed
+ * region).  Shapes that need 2 * (round_up(rows * in_f, 128) + out_f * in_f) bytes above that limit return
+ * GXA_ERR_SHAPE with a message in gxa_last_cuda_error().  All calls on a device share the one array, which keeps the last call's contents (nothing in it
+ * needs to start from zero: both operand regions are overwritten before they are read): calls on one stream are ordered,
+ * calls that overlap on the GPU (different streams without an ordering between them) RACE -- serialise them.
+ * Same result as gxa_linear_fwd(..., GXA_PREC_BF16, workspace, stream). */
+#define GXA_LINEAR_FWD_STATIC_MAX_BYTES (8u << 20)
+int gxa_linear_fwd_static(const float* x, const float* w, const float* b, float* y, int rows, int in_f, int out_f,
+                          void* stream);
 /* dx = dy W (may be NULL); dw += dy^T x; db += colsum(dy) */
 int gxa_linear_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw, float* db, int rows, int in_f,
                    int out_f, int precision, void* workspace, void* stream);
