@@ -14,7 +14,7 @@ repaired equivalent for the path this repository owns:
   inputs ``audio_features`` / ``video_features`` / ``video_mask``, dynamic batch and length axes.  Serialising needs the
   ``onnx`` package (torch's TorchScript exporter imports it in its last step); where it is missing the function says so.
 * ``onnx_graph`` stops one step earlier and returns torch's in-memory ONNX graph plus the initialisers; tests/test_export_gpu.py
-  evaluates that graph node by node and compares it with the CUDA path and the oracle, so the emitted graph is checked
+  evaluates that graph node by node and compares it with the CUDA path and the reference goldens, so the emitted graph is checked
   even where ``onnx`` / ``onnxruntime`` are not installed (this image).
 
 Operators used: Add Sub Mul Div Sqrt Tanh Erf ReduceMean MatMul Transpose Reshape Slice Softmax Where IsNaN Unsqueeze
@@ -90,7 +90,7 @@ def _block_graph(g, x, xa, mask, n_heads, p):
             s = g.op("Add", s, g.op("Where", m4, _const(g, float("-inf")), _const(g, 0.0)))
         prob = g.op("Softmax", s, axis_i=-1)
         if mask is not None:
-            # a sample whose keys are ALL padded: softmax of -inf everywhere is NaN; the library (and the oracle) define
+            # a sample whose keys are ALL padded: softmax of -inf everywhere is NaN; the library (and its CPU checker) define
             # the attention output of such rows as 0
             prob = g.op("Where", g.op("IsNaN", prob), _const(g, 0.0), prob)
         ctx = g.op("Transpose", g.op("MatMul", prob, v), perm_i=[0, 2, 1, 3])
