@@ -188,6 +188,15 @@ int gxa_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int 
                   void* C, int ldc, void* C2, int ldc2, const float* bias, const void* aux, int ld_aux,
                   const float* gate, int accumulate, int bn, int k_splits, void* stream);
 
+/* Few-row linear layer of the decode step (the nn.Linear / in-projection calls of
+ * models/gate_cross_attention.py:40, :43-44 when only R = batch x beams <= 256 query rows are live):
+ * out[R, N] = epilogue(X[R, K] W[N, K]^T + bias), X and W bf16, K % 64 == 0, K >= 128, N % 4 == 0.
+ * epi 0: out bf16;  1: out bf16 = gelu_erf(bf16(.));  2: out f32 = res + tanh(*gate) * (.)  (res f32 [R, ldres]).
+ * Weight tile on the M side of the MMA, K split over a thread-block cluster, partials reduced through distributed
+ * shared memory (csrc/gxa_skinny.cu).  gxa_block_decode uses it for all four projections. */
+int gxa_linear_few_rows_bf16(const void* X, int ldx, const void* W, int ldw, int R, int N, int K, int epi, void* out,
+                             int ldo, const float* bias, const float* res, int ldres, const float* gate, void* stream);
+
 /* Masked-softmax attention over variable-length keys, head_dim 64 (replaces the SDPA call at
  * torch/nn/functional.py:6676-6684).  q: bf16 [B*Lq, ldq]; k,v: bf16 [B*Lk, ldkv] (head h = columns
  * [64h, 64h+64)); ctx: bf16 [B*Lq, ldc]; lse: fp32 [B, H, Lq] (natural log). */

@@ -62,6 +62,7 @@ SIGNATURES = {
     "gxa_linear_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "gxa_linear_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "gxa_linear_bwd": (_i, [_vp] * 6 + [_i, _i, _i, _i, _vp, _vp]),
+    "gxa_linear_few_rows_bf16": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _vp, _vp]),
     "gxa_linear_fwd_static": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "gxa_gemm_bf16": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _i,
                            _vp]),

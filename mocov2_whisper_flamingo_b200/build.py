@@ -19,7 +19,7 @@ CSRC = os.path.join(HERE, "csrc")
 _VARIANT = os.environ.get("GXA_BUILD_VARIANT", "")
 OBJ = os.path.join(HERE, "build" + ("_" + _VARIANT if _VARIANT else ""))
 LIB = os.path.join(HERE, "libgxa_b200." + _VARIANT + ".so" if _VARIANT else "libgxa_b200.so")
-SOURCES = ["gxa_gemm.cu", "gxa_gemm2.cu", "gxa_rowwise.cu", "gxa_attn.cu", "gxa_attn_tc.cu", "gxa_attn_bwd_tc.cu", "gxa_attn_f32.cu", "gxa_api.cu", "gxa_noalloc.cu"]
+SOURCES = ["gxa_gemm.cu", "gxa_gemm2.cu", "gxa_rowwise.cu", "gxa_attn.cu", "gxa_attn_tc.cu", "gxa_attn_bwd_tc.cu", "gxa_attn_f32.cu", "gxa_api.cu", "gxa_noalloc.cu", "gxa_skinny.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC"] + os.environ.get("GXA_NVCC_EXTRA", "").split()     # e.g. -DGXA_BWD_STAMPS (tools/)

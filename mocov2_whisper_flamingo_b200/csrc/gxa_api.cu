@@ -262,6 +262,11 @@ static int gated_residual_small_m(const bf16* A, int K, const bf16* Wt, int M, i
                    DropCfg{0, 1.f, 0, 0}, ks);
 }
 
+// few-row linear layers of the decode step (gxa_skinny.cu): epi 0 bf16(+bias), 1 bias + GELU -> bf16, 2 gated residual f32
+bool skinny_supported(int R, int N, int K);
+int skinny_linear(const void* X, int ldx, const void* W, int ldw, int R, int N, int K, int epi, void* out, int ldo,
+                  const float* bias, const float* res, int ldres, const float* gate, cudaStream_t s);
+
 static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const void* wcache, const float* x,
                           const void* xa_op, const uint8_t* mask, const int32_t* kv_end, float* y, void* saved,
                           cudaStream_t s, const bf16* kv_cached = nullptr) {
@@ -273,6 +278,10 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
   WCache W(d, wcache);
   if (kv_cached != nullptr) S.kv = const_cast<bf16*>(kv_cached);   // ... K|V were projected once (gxa_block_kv_prefill)
   const bool small_m = kv_cached != nullptr && M <= 256 && d.p_drop == 0.f;   // decode step: split-K gated residuals
+  // decode step with <= 256 query rows: all four projections on the cluster split-K kernel (GXA_DECODE_SKINNY=0: A/B)
+  static const bool skinny_on = [] { const char* e = getenv("GXA_DECODE_SKINNY"); return !(e && e[0] == '0'); }();
+  const bool skinny = small_m && skinny_on && skinny_supported(M, D, D) && skinny_supported(M, 4 * D, D) &&
+                      skinny_supported(M, D, 4 * D);
   const float* x1 = x;
   if (d.has_xa) {
     SideStream* sd = kv_cached == nullptr ? side_stream() : nullptr;
@@ -280,12 +289,17 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
       GXA_TRY(gemm_bf16(xa_op, D, false, W.in_proj + size_t(D) * D, D, false, Mk, 2 * D, D, EPI_BF16, S.kv, 2 * D,
                         nullptr, 0, p.in_proj_b + D, nullptr, 0, nullptr, 0, side_fork(sd, 0, s)));
     GXA_TRY(ln_fwd(x, p.attn_ln_w, p.attn_ln_b, S.h, 0, S.mean1, S.rstd1, M, D, s));
-    GXA_TRY(gemm_bf16(S.h, D, false, W.in_proj, D, false, M, D, D, EPI_BF16, S.q, D, nullptr, 0, p.in_proj_b, nullptr, 0,
-                      nullptr, 0, s));
+    if (skinny)
+      GXA_TRY(skinny_linear(S.h, D, W.in_proj, D, M, D, D, 0, S.q, D, p.in_proj_b, nullptr, 0, nullptr, s));
+    else
+      GXA_TRY(gemm_bf16(S.h, D, false, W.in_proj, D, false, M, D, D, EPI_BF16, S.q, D, nullptr, 0, p.in_proj_b, nullptr, 0,
+                        nullptr, 0, s));
     GXA_TRY(side_join(sd, s));
     GXA_TRY(attn_fwd_bf16(S.q, D, S.kv, S.kv + D, 2 * D, mask, kv_end, S.ctx, D, S.lse, d.B, d.H, d.Lq, d.Lk, s,
                           make_drop_cfg(d.p_drop, d.seed, kDropStreamAttn)));
-    if (small_m)
+    if (skinny)
+      GXA_TRY(skinny_linear(S.ctx, D, W.out, D, M, D, D, 2, S.x1, D, p.out_proj_b, x, D, p.attn_gate, s));
+    else if (small_m)
       GXA_TRY(gated_residual_small_m(S.ctx, D, W.out, M, D, p.out_proj_b, x, p.attn_gate, S.x1, s));
     else
       GXA_TRY(gemm_bf16(S.ctx, D, false, W.out, D, false, M, D, D, EPI_GATE_RES, S.x1, D, S.o, D, p.out_proj_b, x, D,
@@ -293,6 +307,10 @@ static int block_fwd_bf16(const gxa_dims& d, const gxa_block_params& p, const vo
     x1 = S.x1;
   }
   GXA_TRY(ln_fwd(x1, p.ff_ln_w, p.ff_ln_b, S.h2, 0, S.mean2, S.rstd2, M, D, s));
+  if (skinny) {
+    GXA_TRY(skinny_linear(S.h2, D, W.ff0, D, M, 4 * D, D, 1, S.a, 4 * D, p.ff0_b, nullptr, 0, nullptr, s));
+    return skinny_linear(S.a, 4 * D, W.ff2, 4 * D, M, D, 4 * D, 2, y, D, p.ff2_b, x1, D, p.ff_gate, s);
+  }
   GXA_TRY(gemm_bf16(S.h2, D, false, W.ff0, D, false, M, 4 * D, D, EPI_BIAS_GELU, S.u, 4 * D, S.a, 4 * D, p.ff0_b, nullptr,
                     0, nullptr, 0, s));
   if (small_m)
@@ -679,6 +697,15 @@ int gxa_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int 
   op.bias = bias; op.aux = aux; op.ld_aux = ld_aux; op.gate = gate; op.accumulate = accumulate;
   op.bn = bn; op.k_splits = k_splits;
   GXA_TRY(gemm_launch(op, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+int gxa_linear_few_rows_bf16(const void* X, int ldx, const void* W, int ldw, int R, int N, int K, int epi, void* out,
+                             int ldo, const float* bias, const float* res, int ldres, const float* gate, void* stream) {
+  if (!X || !W || !out) return GXA_ERR_ARG;
+  if (epi < 0 || epi > 2) return GXA_ERR_UNSUPPORTED;
+  GXA_TRY(skinny_linear(X, ldx, W, ldw, R, N, K, epi, out, ldo, bias, res, ldres, gate,
+                        reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
 

@@ -107,10 +107,23 @@ def _block_graph(g, x, xa, mask, n_heads, p):
 
 # ------------------------------------------------------------------------------------------------ export-time Functions
 # forward = the product's CUDA path (inference, no autograd graph); symbolic = graph emission
+class _no_trace:
+    """The tracer keeps recording aten calls made INSIDE an autograd Function's forward (they are dead code once the
+    Function's node takes over its outputs), and chokes on some of the host-side ones the library makes (dtype views of
+    workspace buffers).  Nothing inside these forwards belongs in the graph: tracing is paused for their duration."""
+
+    def __enter__(self):
+        self.state = torch._C._get_tracing_state()
+        torch._C._set_tracing_state(None)
+
+    def __exit__(self, *exc):
+        torch._C._set_tracing_state(self.state)
+
+
 class _BlockExportFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, xa, mask, n_heads, block, *params):
-        with torch.no_grad():
+        with _no_trace(), torch.no_grad():
             return block(x, xa, mask)
 
     @staticmethod
@@ -121,7 +134,7 @@ class _BlockExportFn(torch.autograd.Function):
 class _LinearExportFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, precision):
-        with torch.no_grad():
+        with _no_trace(), torch.no_grad():
             return LinearFn.apply(x, w, b, precision)
 
     @staticmethod
@@ -132,7 +145,7 @@ class _LinearExportFn(torch.autograd.Function):
 class _LayerNormExportFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b):
-        with torch.no_grad():
+        with _no_trace(), torch.no_grad():
             return LayerNormFn.apply(x, w, b)
 
     @staticmethod
