@@ -549,6 +549,7 @@ def run_product(args, D, H, layers, GB, Lq, Lk, variable):
             out["dp_grad_check"] = dp_check
             out["config"]["grad_exchange"] = "bf16 (GXA_DP_GRAD_DTYPE)" if ddp.grad_dtype is not None else "fp32"
             out["config"]["nccl_max_ctas"] = os.environ.get("NCCL_MAX_CTAS")
+            out["config"]["layers_per_collective"] = ddp.group
     # free the product's model before the baselines (the eager baseline needs ~33 GB at config 3)
     del model, ddp
     torch.cuda.empty_cache()

@@ -232,7 +232,10 @@ class BlockFn(torch.autograd.Function):
         D = dims.D
         dyf = _f32c(dy)
         sizes, offs, total = bucket_layout(D)
-        bucket = torch.zeros(total, dtype=torch.float32, device=xf.device)
+        # the data-parallel hook may hand out the bucket itself (slices of one flat buffer per group of layers)
+        alloc = getattr(getattr(shared.grad_hook, "__self__", None), "alloc_bucket", None)
+        bucket = alloc(ctx.token, total, xf.device) if alloc is not None else \
+            torch.zeros(total, dtype=torch.float32, device=xf.device)
         views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
         pp = BlockPtrs(*[p.data_ptr() for p in pd])
         gp = BlockPtrs(*[v.data_ptr() for v in views])

@@ -69,7 +69,8 @@ def _worker(rank: int, world: int, port: int, average: bool, wire: str = "fp32")
                     p.uniform_(-0.1, 0.1)
         # wire = "bf16": the layer buckets travel as bf16 (torch DDP's bf16_compress_hook equivalent); each contribution is
         # rounded to 8 mantissa bits once and the sum is formed in bf16 -> 2^-8 relative per element at world 2
-        ddp = DataParallelGrads(model, average=average, grad_dtype=torch.bfloat16 if wire == "bf16" else None)
+        ddp = DataParallelGrads(model, average=average, grad_dtype=torch.bfloat16 if wire == "bf16" else None,
+                                group_layers=LAYERS if average else 1)      # grouped (one collective) and per-layer
         tol = 2e-5 if wire == "fp32" else 8e-3
         ddp.broadcast_parameters(src=0)                     # ... and are made identical to rank 0's
         state = {k: v.detach().clone() for k, v in model.state_dict().items()}
@@ -84,8 +85,12 @@ def _worker(rank: int, world: int, port: int, average: bool, wire: str = "fp32")
 
         # what BlockFn.backward does, layer by layer in backward order
         sizes, offs, total = bucket_layout(D)
+        calls = []
+        real_all_reduce = dist.all_reduce
+        dist.all_reduce = lambda t, *a, **k: (calls.append(t.numel()), real_all_reduce(t, *a, **k))[1]
         for i in reversed(range(LAYERS)):
-            bucket = torch.zeros(total)
+            bucket = ddp.alloc_bucket(model.layers[i], total, torch.device("cpu"))    # as BlockFn.backward does
+            assert bucket.numel() == total and not bool(bucket.any())
             views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
             for v, key in zip(views, LAYER_KEYS):
                 v.copy_(local[f"layers.{i}.{key}"])
@@ -93,6 +98,9 @@ def _worker(rank: int, world: int, port: int, average: bool, wire: str = "fp32")
             assert model.grad_hook(model.layers[i], bucket, views) is False
             for v, prm in zip(views, model.layers[i]._params()):
                 prm.grad = v                                                  # ... as AccumulateGrad does
+        dist.all_reduce = real_all_reduce
+        # grouped: the LAYERS buckets are slices of one flat buffer reduced by ONE collective; otherwise one per layer
+        assert calls == ([LAYERS * total] if average else [total] * LAYERS), calls
         for n, prm in model.named_parameters():
             if not n.startswith("layers."):
                 prm.grad = local[n].clone()

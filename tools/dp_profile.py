@@ -2,7 +2,7 @@
 of config 3 (default 8 = the shard of the 8-GPU run), and time on every rank
     plain        no gradient exchange object at all
     ddp-skip     DataParallelGrads attached, collective skipped (GXA_DP_DIAG_NO_ALLREDUCE): hook + SM budget only
-    ddp-fp32     the bench configuration
+    ddp-fp32/gK  fp32 exchange, one collective per K layers (g1 = the bench configuration)
     ddp-bf16     bf16 gradient exchange
 device time per step (CUDA events, max over ranks) and host time to enqueue a step; then a CUPTI timeline of rank 0 for
 ddp-fp32: per-kernel totals, NCCL kernel durations, idle gaps.
@@ -85,8 +85,9 @@ measure("ddp-skip")
 os.environ.pop("GXA_DP_DIAG_NO_ALLREDUCE")
 ddp = DataParallelGrads(model, grad_dtype=torch.bfloat16)
 measure("ddp-bf16")
-ddp = DataParallelGrads(model)
-measure("ddp-fp32")
+for grp in (2, 4, 1):                         # layers per collective (parallel.py "Grouping"); the default comes last
+    ddp = DataParallelGrads(model, group_layers=grp)
+    measure(f"ddp-fp32/g{grp}")
 
 if os.environ.get("TIMELINE", "1") == "1":
     from torch.profiler import ProfilerActivity, profile
