@@ -76,6 +76,44 @@ def bucket_layout(D: int):
 PARAM_SHAPES = lambda D: [(1,), (1,), (3 * D, D), (3 * D,), (D, D), (D,), (D,), (D,), (D,), (D,), (4 * D, D), (4 * D,),
                           (D, 4 * D), (D,)]
 
+# Host time per layer matters at small per-GPU batches (8 ranks on one host: the step is host-bound, tools/dp_profile.py):
+# everything that depends on the shape only is computed once.
+_LAYOUTS: dict = {}
+_SIZES: dict = {}
+
+
+def _layout(D: int):
+    """(sizes, byte offsets, total floats, padded sizes, shapes) of a layer's flat gradient bucket."""
+    lay = _LAYOUTS.get(D)
+    if lay is None:
+        sizes, offs, total = bucket_layout(D)
+        padded = [(s + 63) // 64 * 64 for s in sizes]
+        lay = _LAYOUTS[D] = (sizes, [4 * o for o in offs], total, padded, PARAM_SHAPES(D))
+    return lay
+
+
+def bucket_views(bucket: torch.Tensor, D: int):
+    """The 14 gradient views of a flat bucket: one split call, then only the gates (padded to 64 floats) are sliced and
+    only the four matrices are reshaped."""
+    sizes, _, _, padded, shapes = _layout(D)
+    parts = torch.split_with_sizes(bucket, padded)
+    out = []
+    for part, s, pad, shp in zip(parts, sizes, padded, shapes):
+        if s != pad:
+            part = part[:s]
+        out.append(part.view(shp) if len(shp) > 1 else part)
+    return out
+
+
+def _block_sizes(dims: "Dims"):
+    """(saved bytes, workspace bytes) of a block call, cached by shape."""
+    key = (dims.B, dims.Lq, dims.Lk, dims.D, dims.H, dims.precision, dims.has_xa)
+    v = _SIZES.get(key)
+    if v is None:
+        L = _lib.lib()
+        v = _SIZES[key] = (int(L.gxa_block_saved_bytes(C.byref(dims))), int(L.gxa_block_workspace_bytes(C.byref(dims))))
+    return v
+
 
 class BlockState:
     """Per-module device state: the bf16 operand cache of the weights, refreshed when a weight changes."""
@@ -85,10 +123,23 @@ class BlockState:
         self.key = None
         self.ready = None        # event of a cast enqueued on another stream (prefetch), not yet waited for
         self._event = None
+        self.ptrs = None         # data pointers of the 14 parameters last validated (fp32, contiguous) ...
+        self.pp = None           # ... and their BlockPtrs struct
 
     @staticmethod
     def _key(dims: Dims, params):
         return (dims.precision, dims.D) + tuple((p.data_ptr(), p._version) for p in params)
+
+    def pointers(self, params) -> BlockPtrs:
+        """BlockPtrs of the parameters; dtype / layout are validated when a pointer changed, not on every call."""
+        ptrs = tuple(p.data_ptr() for p in params)
+        if ptrs != self.ptrs:
+            for p in params:
+                if p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError("gxa_b200: block parameters must be contiguous fp32 (the reference's only "
+                                       "supported storage, SURVEY A.1 M8)")
+            self.ptrs, self.pp = ptrs, BlockPtrs(*ptrs)
+        return self.pp
 
     def refresh(self, dims: Dims, params, pp: BlockPtrs, stream: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """(Re)build the bf16 operand cache if a weight changed.  With ``stream`` the cast is enqueued there (the stack
@@ -187,12 +238,8 @@ class BlockFn(torch.autograd.Function):
                                    "(mat1 and mat2 shapes cannot be multiplied)")
         Lk = xa.shape[1] if has_xa else 0
         dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa, p_drop, next_dropout_seed() if p_drop > 0.0 else 0)
-        pd = [p.detach() for p in params]
-        for p in pd:
-            if p.dtype != torch.float32 or not p.is_contiguous():
-                raise RuntimeError("gxa_b200: block parameters must be contiguous fp32 (the reference's only "
-                                   "supported storage, SURVEY A.1 M8)")
-        pp = BlockPtrs(*[p.data_ptr() for p in pd])
+        pd = params                        # inside Function.forward these are plain tensors (no graph is recorded)
+        pp = state.pointers(pd)
         wcache = state.refresh(dims, pd, pp)
         state.wait_ready()
         if has_xa and shared.xa_op is None:
@@ -202,18 +249,18 @@ class BlockFn(torch.autograd.Function):
                   "gxa_xa_prepare")
         if shared.first_token is None:
             shared.first_token = token
-        nsaved = L.gxa_block_saved_bytes(C.byref(dims))
+        nsaved, nws = _block_sizes(dims)
         if nsaved == 0:
             raise RuntimeError(f"gxa_b200: unsupported shape B={B} Lq={Lq} Lk={Lk} D={D} H={n_heads} "
                                "(need head_dim 64 and d_model % 128 == 0)")
         saved = torch.empty(nsaved, dtype=torch.uint8, device=x.device)
-        ws = workspace(L.gxa_block_workspace_bytes(C.byref(dims)), x.device)
+        ws = workspace(nws, x.device)
         y = torch.empty_like(xf)
         check(L.gxa_block_fwd(C.byref(dims), C.byref(pp), wcache.data_ptr(), xf.data_ptr(), _p(shared.xa_op),
                               _p(shared.mask_u8), _p(shared.kv_end), y.data_ptr(), saved.data_ptr(), ws.data_ptr(),
                               _stream()), "gxa_block_fwd")
         ctx.dims, ctx.shared, ctx.state, ctx.token = dims, shared, state, token
-        ctx.wcache = wcache
+        ctx.wcache, ctx.pp = wcache, pp
         ctx.xa_shape = tuple(xa.shape) if has_xa else None
         ctx.xa_needs_grad = bool(has_xa and ctx.needs_input_grad[1])
         if ctx.xa_needs_grad:
@@ -231,21 +278,22 @@ class BlockFn(torch.autograd.Function):
         dims, shared = ctx.dims, ctx.shared
         D = dims.D
         dyf = _f32c(dy)
-        sizes, offs, total = bucket_layout(D)
+        _, boffs, total, _, _ = _layout(D)
         # the data-parallel hook may hand out the bucket itself (slices of one flat buffer per group of layers)
         alloc = getattr(getattr(shared.grad_hook, "__self__", None), "alloc_bucket", None)
         bucket = alloc(ctx.token, total, xf.device) if alloc is not None else \
             torch.zeros(total, dtype=torch.float32, device=xf.device)
-        views = [bucket[o:o + s].view(shp) for s, o, shp in zip(sizes, offs, PARAM_SHAPES(D))]
-        pp = BlockPtrs(*[p.data_ptr() for p in pd])
-        gp = BlockPtrs(*[v.data_ptr() for v in views])
+        views = bucket_views(bucket, D)
+        pp = ctx.pp                                # saved tensors are the parameters themselves: same storage as in forward
+        base = bucket.data_ptr()
+        gp = BlockPtrs(*[base + o for o in boffs])
         dx = torch.empty_like(xf)
         dxa_ptr = None
         if dims.has_xa and shared.dxa_wanted:      # xa without requires_grad: the d(xa) GEMM is not run at all
             if shared.dxa is None:
                 shared.dxa = torch.zeros(ctx.xa_shape, dtype=torch.float32, device=xf.device)
             dxa_ptr = shared.dxa.data_ptr()
-        ws = workspace(L.gxa_block_workspace_bytes(C.byref(dims)), xf.device)
+        ws = workspace(_block_sizes(dims)[1], xf.device)
         check(L.gxa_block_bwd(C.byref(dims), C.byref(pp), ctx.wcache.data_ptr(), xf.data_ptr(), _p(shared.xa_op),
                               _p(shared.mask_u8), _p(shared.kv_end), saved.data_ptr(), dyf.data_ptr(),
                               dx.data_ptr(), dxa_ptr, C.byref(gp), ws.data_ptr(), _stream()), "gxa_block_bwd")

@@ -121,20 +121,21 @@ class GatedCrossModalFusion(nn.Module):
             return
         stale = []
         for layer in self.layers:
-            pd = [p.detach() for p in layer._params()]
-            dims = _dims(1, 1, 1, layer.d_model, layer.n_heads, prec, True)
-            if layer._state.wcache is None or layer._state.key != BlockState._key(dims, pd):
-                stale.append((layer, dims, pd))
+            pd = layer._params()
+            st = layer._state
+            if st.wcache is None or st.key != (prec, layer.d_model) + tuple((p.data_ptr(), p._version) for p in pd):
+                stale.append((layer, pd))
         if not stale:
             return
         side = self._cast_streams.get(device.index)
         if side is None:
             side = self._cast_streams[device.index] = torch.cuda.Stream(device=device)
         side.wait_stream(torch.cuda.current_stream(device))
-        for layer, dims, pd in stale:
-            if any(p.dtype != torch.float32 or not p.is_contiguous() or not p.is_cuda for p in pd):
+        for layer, pd in stale:
+            if any(not p.is_cuda for p in pd):
                 return                     # BlockFn.forward raises the proper error
-            layer._state.refresh(dims, pd, BlockPtrs(*[p.data_ptr() for p in pd]), stream=side)
+            dims = _dims(1, 1, 1, layer.d_model, layer.n_heads, prec, True)
+            layer._state.refresh(dims, pd, layer._state.pointers(pd), stream=side)
 
     def forward(self, audio_features, video_features, audio_mask=None, video_mask=None):
         _log_shapes(self.enable_logging, "fusion in", audio_features=audio_features, video_features=video_features)

@@ -23,13 +23,16 @@ already present (gradient accumulation -- the reference trains with accumulate_g
 ``no_sync()`` (as torch DDP's) skips the collective for the micro-batches inside it; the all-reduce of the last
 micro-batch then carries the accumulated sum.  Call ``finish()`` before ``optimizer.step()`` / ``zero_grad``.
 
-Grouping (optional).  Every collective costs the host ~115 us of torch.distributed / NCCL enqueue work (tools/dp_profile.py
-at 8 samples per GPU: host enqueue 10.6 -> 13.6 ms per step with 24 per-layer collectives).  ``alloc_bucket`` can hand
+Grouping.  Every collective costs the host ~115 us of torch.distributed / NCCL enqueue work.  ``alloc_bucket`` can hand
 ``group_layers`` consecutive layers slices of ONE flat buffer, reduced once when the group's lowest layer has produced
-its gradients.  Measured at N = 2, 8 samples per GPU: host time 13.6 -> 12.2 (2 layers) / 11.9 ms (4), but the DEVICE time
-rises 14.25 -> 14.50 / 14.65 ms -- the larger last collective sits behind the end of backward -- and the device is what
-bounds the step, so the default stays one collective per layer (GXA_DP_GROUP / ``group_layers`` = 1); a host-bound
-deployment (slower CPU, more ranks per socket) can raise it.
+its gradients: fewer collectives, at the price of a larger last collective behind the end of backward.  Measured with
+tools/dp_profile.py at 8 samples per GPU (config 3's shard on 8 GPUs), device ms per step / host enqueue ms per step:
+    N = 2:  1 layer per collective 14.25 / 13.6,  2: 14.50 / 12.2,  4: 14.65 / 11.9   -> device-bound, grouping costs
+    N = 8:  1 layer per collective 16.12 / 13.9,  2: 14.91 / 13.6,  4: 15.14 / 13.0   -> eight processes on one host
+            enqueue ~30 % slower each (13.65 ms without any collective against 10.6 at N = 2) and the step is host-bound
+Default: 2 layers per collective on 8 or more ranks, 1 below (GXA_DP_GROUP / ``group_layers`` override it).  Only the
+common path is grouped (no gradient present at backward: the first micro-batch after zero_grad(set_to_none=True)); layers
+that accumulate into existing gradients are reduced one by one as before.
 
 SM budget: the NCCL kernel keeps its CTAs (NCCL_MAX_CTAS) resident while a bucket is in flight.  The library's
 persistent kernels partition their work statically over the CTAs they launch, so a CTA that has to wait for an SM held
@@ -61,8 +64,8 @@ class DataParallelGrads:
         self.require_sync = True
         self._home: Dict[int, tuple] = {}              # id(layer) -> (flat bucket its p.grad are views of, their data_ptrs)
         self._touched: List[torch.Tensor] = []
-        if group_layers is None:
-            group_layers = int(os.environ.get("GXA_DP_GROUP", "1"))
+        if group_layers is None:               # measured default: 2 layers per collective on 8 ranks, 1 below (see above)
+            group_layers = int(os.environ.get("GXA_DP_GROUP", "2" if self.world >= 8 else "1"))
         self.group = max(1, group_layers)
         self._index = {id(layer): i for i, layer in enumerate(fusion.layers)}
         self._gbuf: Optional[torch.Tensor] = None      # flat buffer of the group of layers in flight

@@ -47,10 +47,12 @@ for _ in range(4):
 torch.cuda.synchronize()
 ddp = None
 
+plist = list(model.parameters())
+
 
 def step():
     model.invalidate_weight_cache()
-    model.zero_grad(set_to_none=True)
+    bench.drop_grads(plist)
     a.grad = v.grad = None
     y = model(a, v, video_mask=mask)
     (y * dy).sum().backward()

@@ -34,10 +34,12 @@ v = torch.randn(B, Lk, D, device="cuda", requires_grad=True)
 mask = torch.zeros(B, Lk, dtype=torch.bool, device="cuda")
 dy = torch.randn(B, Lq, D, device="cuda")
 
+plist = list(model.parameters())
+
 
 def step():
     model.invalidate_weight_cache()
-    model.zero_grad(set_to_none=True)
+    bench.drop_grads(plist)
     a.grad = v.grad = None
     y = model(a, v, video_mask=mask)
     (y * dy).sum().backward()
