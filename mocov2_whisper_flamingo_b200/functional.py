@@ -32,7 +32,15 @@ def resolve_precision(pref: Optional[int] = None) -> int:
     return GXA_PREC_BF16 if torch.is_autocast_enabled("cuda") else GXA_PREC_FP32
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_raw_device = getattr(torch._C, "_cuda_getDevice", None)
+
+
 def _stream() -> int:
+    """cudaStream_t of torch's current stream on the current device.  The raw accessor is ~20x cheaper than building a
+    torch.cuda.Stream object, and this is called ~130 times per step (host time matters at small batches)."""
+    if _raw_stream is not None and _raw_device is not None:
+        return _raw_stream(_raw_device())
     return torch.cuda.current_stream().cuda_stream
 
 

@@ -6,7 +6,6 @@ set -x
 TIMELINE=0 run 29541 tools/dp_profile.py > $out/${tag}_dp_profile_n$N.txt 2>&1
 run 29542 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu-baseline --no-gpu-baseline > $out/${tag}_scale_n$N.json 2> $out/${tag}_scale_n$N.err
 if [ "$3" == "c4" ]; then
-  GXA_DP_GROUP=2 run 29543 bench.py --gpus $N --steps 20 --warmup 5 --no-cpu-baseline --no-gpu-baseline > $out/${tag}_scale_n${N}_group2.json 2> $out/${tag}_scale_n${N}_group2.err
   run 29544 bench.py --gpus $N --workload whisper-large-c4 --steps 10 --warmup 3 --no-cpu-baseline --no-gpu-baseline > $out/${tag}_c4_n${N}_contiguous.json 2> $out/${tag}_c4_contig.err
   run 29545 bench.py --gpus $N --workload whisper-large-c4 --shards balanced --steps 10 --warmup 3 --no-cpu-baseline --no-gpu-baseline > $out/${tag}_c4_n${N}_balanced.json 2> $out/${tag}_c4_bal.err
 fi
