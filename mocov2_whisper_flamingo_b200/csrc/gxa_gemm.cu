@@ -1,4 +1,7 @@
 // tcgen05 GEMM kernel + host launcher (tensor-map construction, dispatch).
+#include <cstdlib>
+#include <mutex>
+
 #include "gxa_gemm.cuh"
 #include "gxa_host.h"
 
@@ -175,11 +178,63 @@ static int get_encode() {
   return 0;
 }
 
+// Descriptor cache.  A training step encodes ~1000 tensor maps (2-3 per GEMM, 18 GEMMs per layer) and the caching allocator
+// hands the same buffers back step after step, so nearly every encode repeats an earlier one; cuTensorMapEncodeTiled is a
+// driver call of 1-2 us, which is host time the 8-samples-per-GPU step does not have.  Direct-mapped, keyed by every
+// argument of the encode; a tensor map is a pure function of those arguments (it holds no reference to the memory).
+struct TmapKey {
+  const void* base;
+  uint64_t inner, outer, ld;
+  uint32_t box_inner, box_outer, kind, pad;
+  uint64_t outer2, ld2;          // third dimension of the 3-D maps (0 otherwise)
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && box_inner == o.box_inner &&
+           box_outer == o.box_outer && kind == o.kind && outer2 == o.outer2 && ld2 == o.ld2;
+  }
+};
+struct TmapSlot {
+  TmapKey key;
+  CUtensorMap map;
+  bool valid;
+};
+constexpr int kTmapSlots = 4096;
+static TmapSlot* g_tmap_cache = nullptr;
+static std::mutex g_tmap_mu;
+static const bool g_tmap_cache_on = [] { const char* e = getenv("GXA_TMAP_CACHE"); return !(e && e[0] == '0'); }();
+
+static inline size_t tmap_hash(const TmapKey& k) {
+  uint64_t h = reinterpret_cast<uint64_t>(k.base) * 0x9E3779B97F4A7C15ull;
+  h ^= (k.inner * 0xC2B2AE3D27D4EB4Full) ^ (k.outer * 0x165667B19E3779F9ull) ^ (k.ld << 17) ^
+       (uint64_t(k.box_inner) << 40) ^ (uint64_t(k.box_outer) << 48) ^ (uint64_t(k.kind) << 56) ^
+       (k.outer2 * 0x27D4EB2F165667C5ull) ^ (k.ld2 << 7);
+  return static_cast<size_t>((h ^ (h >> 29)) % kTmapSlots);
+}
+static bool tmap_lookup(const TmapKey& k, CUtensorMap* out) {
+  if (!g_tmap_cache_on) return false;
+  std::lock_guard<std::mutex> lk(g_tmap_mu);
+  if (!g_tmap_cache) return false;
+  const TmapSlot& s = g_tmap_cache[tmap_hash(k)];
+  if (!s.valid || !(s.key == k)) return false;
+  *out = s.map;
+  return true;
+}
+static void tmap_store(const TmapKey& k, const CUtensorMap& m) {
+  if (!g_tmap_cache_on) return;
+  std::lock_guard<std::mutex> lk(g_tmap_mu);
+  if (!g_tmap_cache) g_tmap_cache = new TmapSlot[kTmapSlots]();
+  TmapSlot& s = g_tmap_cache[tmap_hash(k)];
+  s.key = k;
+  s.map = m;
+  s.valid = true;
+}
+
 // 2-D bf16 tensor map: `inner` contiguous elements, `outer` rows `ld` elements apart.
 int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
                    uint32_t box_outer) {
   if (int e = get_encode()) return e;
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld * 2) % 16) return GXA_ERR_ALIGN;
+  const TmapKey key{base, inner, outer, ld, box_inner, box_outer, 1u, 0u, 0, 0};
+  if (tmap_lookup(key, m)) return 0;
   cuuint64_t dims[2] = {inner, outer};
   cuuint64_t strides[1] = {ld * 2};
   cuuint32_t box[2] = {box_inner, box_outer};
@@ -187,7 +242,9 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t ou
   CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : GXA_ERR_TMAP;
+  if (r != CUDA_SUCCESS) return GXA_ERR_TMAP;
+  tmap_store(key, *m);
+  return 0;
 }
 
 
@@ -196,6 +253,8 @@ int make_tmap_f32_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t 
                      uint32_t box_outer) {
   if (int e = get_encode()) return e;
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld * 4) % 16) return GXA_ERR_ALIGN;
+  const TmapKey key{base, inner, outer, ld, box_inner, box_outer, 2u, 0u, 0, 0};
+  if (tmap_lookup(key, m)) return 0;
   cuuint64_t dims[2] = {inner, outer};
   cuuint64_t strides[1] = {ld * 4};
   cuuint32_t box[2] = {box_inner, box_outer};
@@ -203,7 +262,9 @@ int make_tmap_f32_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t 
   CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : GXA_ERR_TMAP;
+  if (r != CUDA_SUCCESS) return GXA_ERR_TMAP;
+  tmap_store(key, *m);
+  return 0;
 }
 
 // 3-D bf16 tensor map [d2][d1][d0] (d0 contiguous): box {b0, b1, 1}, 128B swizzle, OOB rows read as zero.
@@ -211,6 +272,8 @@ int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1
                       uint64_t ld2, uint32_t b0, uint32_t b1) {
   if (int e = get_encode()) return e;
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld1 * 2) % 16 || (ld2 * 2) % 16) return GXA_ERR_ALIGN;
+  const TmapKey key{base, d0, d1, ld1, b0, b1, 3u, 0u, d2, ld2};
+  if (tmap_lookup(key, m)) return 0;
   cuuint64_t dims[3] = {d0, d1, d2};
   cuuint64_t strides[2] = {ld1 * 2, ld2 * 2};
   cuuint32_t box[3] = {b0, b1, 1};
@@ -218,7 +281,9 @@ int make_tmap_bf16_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1
   CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : GXA_ERR_TMAP;
+  if (r != CUDA_SUCCESS) return GXA_ERR_TMAP;
+  tmap_store(key, *m);
+  return 0;
 }
 
 template <int BN, int EPI, bool A_MN, bool B_MN>

@@ -80,16 +80,23 @@ def measure(name, steps=10):
               f"(max over ranks; NCCL_MAX_CTAS={os.environ.get('NCCL_MAX_CTAS')})", flush=True)
 
 
-measure("plain")
-os.environ["GXA_DP_DIAG_NO_ALLREDUCE"] = "1"
-ddp = DataParallelGrads(model)
-measure("ddp-skip")
-os.environ.pop("GXA_DP_DIAG_NO_ALLREDUCE")
-ddp = DataParallelGrads(model, grad_dtype=torch.bfloat16)
-measure("ddp-bf16")
-for grp in (2, 4, 1):                         # layers per collective (parallel.py "Grouping"); the default comes last
-    ddp = DataParallelGrads(model, group_layers=grp)
-    measure(f"ddp-fp32/g{grp}")
+# DP_CONFIGS=plain,skip,bf16,g1,g2,g4,g2/sms8,...   gK = K layers per collective, /smsS = SMs taken from the library's
+# persistent grids while buckets are in flight (default NCCL_MAX_CTAS)
+configs = os.environ.get("DP_CONFIGS", "plain,skip,bf16,g2,g4,g1").split(",")
+for cfg in configs:
+    if cfg == "plain":
+        ddp = None
+        model.grad_hook = None
+    elif cfg == "skip":
+        os.environ["GXA_DP_DIAG_NO_ALLREDUCE"] = "1"
+        ddp = DataParallelGrads(model)
+        os.environ.pop("GXA_DP_DIAG_NO_ALLREDUCE")
+    elif cfg == "bf16":
+        ddp = DataParallelGrads(model, grad_dtype=torch.bfloat16)
+    else:
+        grp, _, sms = cfg.partition("/sms")
+        ddp = DataParallelGrads(model, group_layers=int(grp[1:]), comm_sms=int(sms) if sms else None)
+    measure("ddp-" + cfg if cfg != "plain" else cfg)
 
 if os.environ.get("TIMELINE", "1") == "1":
     from torch.profiler import ProfilerActivity, profile
