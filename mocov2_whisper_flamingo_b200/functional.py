@@ -190,6 +190,7 @@ class StackShared:
         self.dxa_wanted = False      # some layer saw xa.requires_grad
         self.first_token = None      # identity of the first block call (its backward runs last)
         self.grad_hook = grad_hook   # callable(layer_token, flat_bucket) -> None (data-parallel all-reduce)
+        self.seeds = None            # dropout seeds drawn for the whole stack (one per layer), consumed by BlockFn.forward
         L = _lib.lib()
         if xa is not None:
             if xa.dim() == 4 and xa.size(1) == 1:
@@ -220,6 +221,13 @@ def next_dropout_seed() -> int:
     return ((hi << 33) ^ (lo << 2) ^ 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
 
 
+def draw_dropout_seeds(n: int) -> list:
+    """n seeds from ONE draw of the same generator (a stack draws its layers' seeds together: one small torch call per
+    forward instead of one per layer)."""
+    v = torch.randint(0, 1 << 31, (2 * n,), dtype=torch.int64).tolist()
+    return [((v[2 * i] << 33) ^ (v[2 * i + 1] << 2) ^ 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF for i in range(n)]
+
+
 class BlockFn(torch.autograd.Function):
     """GatedCrossAttentionBlock.forward / backward (reference: models/gate_cross_attention.py:28-50)."""
 
@@ -245,7 +253,10 @@ class BlockFn(torch.autograd.Function):
                 raise RuntimeError(f"key / value feature width {xa.shape[2]} does not match embed_dim {D} "
                                    "(mat1 and mat2 shapes cannot be multiplied)")
         Lk = xa.shape[1] if has_xa else 0
-        dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa, p_drop, next_dropout_seed() if p_drop > 0.0 else 0)
+        seed = 0
+        if p_drop > 0.0:
+            seed = shared.seeds.pop() if shared.seeds else next_dropout_seed()
+        dims = _dims(B, Lq, Lk, D, n_heads, shared.precision, has_xa, p_drop, seed)
         pd = params                        # inside Function.forward these are plain tensors (no graph is recorded)
         pp = state.pointers(pd)
         wcache = state.refresh(dims, pd, pp)

@@ -24,7 +24,7 @@ import torch
 import torch.nn as nn
 
 from ._lib import BlockPtrs, GXA_PREC_BF16
-from .functional import (BlockFn, BlockState, LayerNormFn, LinearFn, StackShared, _dims, resolve_precision,
+from .functional import (BlockFn, BlockState, LayerNormFn, LinearFn, StackShared, _dims, draw_dropout_seeds, resolve_precision,
                          set_default_precision)
 
 logger = logging.getLogger(__name__)
@@ -148,6 +148,8 @@ class GatedCrossModalFusion(nn.Module):
         xa = LinearFn.apply(video_features, self.video_proj.weight, self.video_proj.bias, prec)
         _log_shapes(self.enable_logging, "fusion projected", x=x, xa=xa)
         shared = StackShared(xa, video_mask, prec, grad_hook=self.grad_hook)
+        if self.training and any(layer.dropout > 0.0 for layer in self.layers):
+            shared.seeds = draw_dropout_seeds(len(self.layers))
         for layer in self.layers:
             x = layer(x, xa, video_mask, _shared=shared)
         x = LayerNormFn.apply(x, self.ln_post.weight, self.ln_post.bias)
