@@ -30,7 +30,7 @@ tools/dp_profile.py at 8 samples per GPU (config 3's shard on 8 GPUs), device ms
     N = 2:  1 layer per collective 14.25 / 13.6,  2: 14.50 / 12.2,  4: 14.65 / 11.9   -> device-bound, grouping costs
     N = 8:  1 layer per collective 16.12 / 13.9,  2: 14.91 / 13.6,  4: 15.14 / 13.0   -> eight processes on one host
             enqueue ~30 % slower each (13.65 ms without any collective against 10.6 at N = 2) and the step is host-bound
-Default: 2 layers per collective on 8 or more ranks, 1 below (GXA_DP_GROUP / ``group_layers`` override it).  Only the
+Default: 2 layers per collective on 4 or more ranks (N = 4, 16 samples per GPU: 24.04 vs 24.21 ms), 1 below (GXA_DP_GROUP / ``group_layers`` override it).  Only the
 common path is grouped (no gradient present at backward: the first micro-batch after zero_grad(set_to_none=True)); layers
 that accumulate into existing gradients are reduced one by one as before.
 
@@ -64,8 +64,8 @@ class DataParallelGrads:
         self.require_sync = True
         self._home: Dict[int, tuple] = {}              # id(layer) -> (flat bucket its p.grad are views of, their data_ptrs)
         self._touched: List[torch.Tensor] = []
-        if group_layers is None:               # measured default: 2 layers per collective on 8 ranks, 1 below (see above)
-            group_layers = int(os.environ.get("GXA_DP_GROUP", "2" if self.world >= 8 else "1"))
+        if group_layers is None:               # measured default: 2 layers per collective on >= 4 ranks, 1 below (see above)
+            group_layers = int(os.environ.get("GXA_DP_GROUP", "2" if self.world >= 4 else "1"))
         self.group = max(1, group_layers)
         self._index = {id(layer): i for i, layer in enumerate(fusion.layers)}
         self._gbuf: Optional[torch.Tensor] = None      # flat buffer of the group of layers in flight
