@@ -45,6 +45,12 @@ def step():
     (y * dy).sum().backward()
 
 
+# HIPRI=1: run the step on a high-priority torch stream (the library's side stream has the default = lowest priority, so
+# its weight-gradient GEMMs then only take SMs the dependency chain does not want)
+if os.environ.get("HIPRI"):
+    _hp = torch.cuda.Stream(priority=-1)
+    _hp.wait_stream(torch.cuda.current_stream())
+    torch.cuda.set_stream(_hp)
 for _ in range(3):
     step()
 torch.cuda.synchronize()
