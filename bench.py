@@ -28,12 +28,28 @@ import json
 import os
 
 os.environ.setdefault("NCCL_MAX_CTAS", "16")   # bound the SMs the gradient all-reduce may hold (parallel.py: SM budget)
-# stdout carries exactly ONE JSON line: NCCL's own banner ("NCCL version ...", printed at NCCL_DEBUG=VERSION) goes to stderr
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"
 import statistics
 import subprocess
 import sys
+
+# stdout carries exactly ONE JSON line.  Native libraries write to file descriptor 1 behind Python's back (NCCL prints its
+# "NCCL version ..." banner there whenever NCCL_DEBUG is VERSION or above, whatever NCCL_DEBUG_FILE says), so descriptor 1
+# is pointed at stderr for the whole run and the result line goes to a private duplicate of the original stdout.
+RESULT_OUT = sys.stdout
+
+
+def claim_stdout() -> None:
+    """Called first thing in main(): from here on only emit_result() reaches the process's stdout."""
+    global RESULT_OUT
+    sys.stdout.flush()
+    RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit_result(obj) -> None:
+    """The one JSON line of this run, on the process's ORIGINAL stdout."""
+    RESULT_OUT.write(json.dumps(obj) + "\n")
+    RESULT_OUT.flush()
 import threading
 import time
 
@@ -243,7 +259,7 @@ def run_reference(args, D, H, layers, GB, Lq, Lk, variable):
         step()
     t = (time.perf_counter() - t0) / args.steps
     value = sample_B * Lq / t
-    print(json.dumps({
+    emit_result({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -251,7 +267,7 @@ def run_reference(args, D, H, layers, GB, Lq, Lk, variable):
                    "Lq": Lq, "Lk": Lk, "dropout": args.dropout, "mode": "train", "sample_batch": sample_B},
         "cpu_baseline": {"value": value, "unit": "tokens/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def gpu_baseline(D, H, layers, B, Lq, Lk, lengths, dropout, steps=3, warmup=2):
@@ -588,12 +604,13 @@ def run_product(args, D, H, layers, GB, Lq, Lk, variable):
             t = statistics.median(ts)
             out["cpu_baseline"] = {"value": args.ref_batch * Lq / t, "unit": "tokens/s", "cores": threads, "kind": kind,
                                    "sample": sample + "; median of 3 after 1 warm-up", "seconds_per_step": t}
-        print(json.dumps(out))
+        emit_result(out)
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
