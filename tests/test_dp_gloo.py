@@ -99,9 +99,9 @@ def _worker(rank: int, world: int, port: int, average: bool, wire: str = "fp32")
             for v, prm in zip(views, model.layers[i]._params()):
                 prm.grad = v                                                  # ... as AccumulateGrad does
         dist.all_reduce = real_all_reduce
-        # grouped: layers 3 and 2 are slices of one flat buffer reduced by ONE collective, the two lowest layers (nothing
-        # left to hide their collective behind) go one by one; ungrouped: one collective per layer
-        assert calls == ([2 * total, total, total] if average else [total] * LAYERS), calls
+        # grouped: layers (3, 2) and (1, 0) are slices of one flat buffer each, reduced by ONE collective per pair;
+        # ungrouped: one collective per layer
+        assert calls == ([2 * total, 2 * total] if average else [total] * LAYERS), calls
         for n, prm in model.named_parameters():
             if not n.startswith("layers."):
                 prm.grad = local[n].clone()
