@@ -256,6 +256,47 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
                                                   const uint32_t (&r)[32], float gate_t, bool first_split, int lane,
                                                   const AuxRegs<EPI>& ax, const CUtensorMap* tmC = nullptr) {
   const uint32_t sbase = smem_u32(stage);
+  if constexpr (EPI == EPI_BF16) {
+    // bf16-first: bias, rounding and packing happen in the TMEM layout (thread = row; the 32 bias values of the chunk are
+    // the same for every lane), so the transpose moves a 2 KB bf16 tile instead of the 4 KB fp32 one.  The staging
+    // traffic goes through the same shared-memory port as the MMA operands and the TMA writes: at
+    // K = 1024 the fp32 transposes were +20 % on that port.  Rows are 64 B here; 16-byte slot j of row l sits at
+    // j ^ ((l >> 1) & 3), which keeps both the row-wise stores and the 4-lanes-per-row loads conflict-free.
+    uint32_t pk[16];
+    if (p.bias != nullptr && first_split) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col) + j);
+        pk[2 * j] = pack_bf16(__uint_as_float(r[4 * j]) + b.x, __uint_as_float(r[4 * j + 1]) + b.y);
+        pk[2 * j + 1] = pack_bf16(__uint_as_float(r[4 * j + 2]) + b.z, __uint_as_float(r[4 * j + 3]) + b.w);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t a = sbase + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pk[4 * j]), "r"(pk[4 * j + 1]),
+                   "r"(pk[4 * j + 2]), "r"(pk[4 * j + 3])
+                   : "memory");
+    }
+    __syncwarp();
+    const int cl4 = lane & 3, rsub8 = lane >> 2;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int rr = it * 8 + rsub8;
+      const int row = row0 + rr;
+      uint4 v;
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                   : "r"(sbase + rr * 64 + ((cl4 ^ ((rr >> 1) & 3)) << 4)));
+      if (row < p.M)
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col + cl4 * 8) = v;
+    }
+    __syncwarp();          // the next chunk re-uses the staging buffer
+    return;
+  }
   if constexpr (EPI == EPI_F32) {
     // the previous chunk's TMA reduction must have finished READING this staging buffer
     if (tmC != nullptr) {
