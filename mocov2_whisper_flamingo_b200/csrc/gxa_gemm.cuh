@@ -227,26 +227,29 @@ struct AuxRegs {};
 template <>
 struct AuxRegs<EPI_GATE_RES> { float4 v[8]; };
 template <>
-struct AuxRegs<EPI_GELU_BWD> { uint2 v[8]; };
+struct AuxRegs<EPI_GELU_BWD> { uint4 v[4]; };     // bf16-first layout: 4 lanes per row, 8 columns (16 B) per lane
 
 template <int EPI>
 __device__ __forceinline__ void aux_prefetch(const GemmParams& p, int row0, int col, int lane, AuxRegs<EPI>& ax) {
-  if constexpr (EPI == EPI_GATE_RES || EPI == EPI_GELU_BWD) {
+  if constexpr (EPI == EPI_GATE_RES) {
     const int c = col + 4 * (lane & 7), rsub = lane >> 3;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int row = row0 + it * 4 + rsub;
-      if constexpr (EPI == EPI_GATE_RES) {
-        ax.v[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row < p.M)
-          ax.v[it] = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) +
-                                                          static_cast<size_t>(row) * p.ld_aux + c));
-      } else {
-        ax.v[it] = make_uint2(0u, 0u);
-        if (row < p.M)
-          ax.v[it] = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
-                                                         static_cast<size_t>(row) * p.ld_aux + c));
-      }
+      ax.v[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row < p.M)
+        ax.v[it] = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.aux) +
+                                                        static_cast<size_t>(row) * p.ld_aux + c));
+    }
+  } else if constexpr (EPI == EPI_GELU_BWD) {
+    const int c = col + 8 * (lane & 3), rsub8 = lane >> 2;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int row = row0 + it * 8 + rsub8;
+      ax.v[it] = make_uint4(0u, 0u, 0u, 0u);
+      if (row < p.M)
+        ax.v[it] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.aux) +
+                                                       static_cast<size_t>(row) * p.ld_aux + c));
     }
   }
 }
@@ -256,14 +259,17 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
                                                   const uint32_t (&r)[32], float gate_t, bool first_split, int lane,
                                                   const AuxRegs<EPI>& ax, const CUtensorMap* tmC = nullptr) {
   const uint32_t sbase = smem_u32(stage);
-  if constexpr (EPI == EPI_BF16) {
+  if constexpr (EPI == EPI_BF16 || EPI == EPI_GELU_BWD) {
     // bf16-first: bias, rounding and packing happen in the TMEM layout (thread = row; the 32 bias values of the chunk are
     // the same for every lane), so the transpose moves a 2 KB bf16 tile instead of the 4 KB fp32 one.  The staging
     // traffic goes through the same shared-memory port as the MMA operands and the TMA writes: at
     // K = 1024 the fp32 transposes were +20 % on that port.  Rows are 64 B here; 16-byte slot j of row l sits at
     // j ^ ((l >> 1) & 3), which keeps both the row-wise stores and the 4-lanes-per-row loads conflict-free.
+    // EPI_GELU_BWD: the staged tile is bf16(acc) (the rounding point of autocast's bf16 linear output); gelu'(u) (aux,
+    // prefetched in the post-transpose layout) multiplies it after the transpose, and the column sums of the rounded
+    // products (= d ff.0.bias) are folded over the 8 row lanes of each column group.
     uint32_t pk[16];
-    if (p.bias != nullptr && first_split) {
+    if (EPI == EPI_BF16 && p.bias != nullptr && first_split) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col) + j);
@@ -283,6 +289,7 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
     }
     __syncwarp();
     const int cl4 = lane & 3, rsub8 = lane >> 2;
+    float cs8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const int rr = it * 8 + rsub8;
@@ -291,12 +298,38 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
       asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
                    : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                    : "r"(sbase + rr * 64 + ((cl4 ^ ((rr >> 1) & 3)) << 4)));
+      if constexpr (EPI == EPI_GELU_BWD) {
+        const uint4 g = ax.v[it];              // gelu'(u), stored by the forward epilogue (zero for rows past M)
+        const float4 a0 = unpack_bf16x4(make_uint2(v.x, v.y)), a1 = unpack_bf16x4(make_uint2(v.z, v.w));
+        const float4 g0 = unpack_bf16x4(make_uint2(g.x, g.y)), g1 = unpack_bf16x4(make_uint2(g.z, g.w));
+        const uint2 o0 = pack_bf16x4(make_float4(a0.x * g0.x, a0.y * g0.y, a0.z * g0.z, a0.w * g0.w));
+        const uint2 o1 = pack_bf16x4(make_float4(a1.x * g1.x, a1.y * g1.y, a1.z * g1.z, a1.w * g1.w));
+        v = make_uint4(o0.x, o0.y, o1.x, o1.y);
+        if (row < p.M) {
+          const float4 s0 = unpack_bf16x4(o0), s1 = unpack_bf16x4(o1);
+          cs8[0] += s0.x; cs8[1] += s0.y; cs8[2] += s0.z; cs8[3] += s0.w;
+          cs8[4] += s1.x; cs8[5] += s1.y; cs8[6] += s1.z; cs8[7] += s1.w;
+        }
+      }
       if (row < p.M)
         *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col + cl4 * 8) = v;
     }
+    if constexpr (EPI == EPI_GELU_BWD) {
+      if (p.colsum != nullptr) {      // 32 rows of this chunk -> one vector reduction per 8 columns
+#pragma unroll
+        for (int o = 4; o <= 16; o <<= 1) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) cs8[k] += __shfl_xor_sync(0xffffffffu, cs8[k], o);
+        }
+        if (rsub8 == 0) {
+          float* dst = p.colsum + col + cl4 * 8;
+          atomicAdd(reinterpret_cast<float4*>(dst), make_float4(cs8[0], cs8[1], cs8[2], cs8[3]));
+          atomicAdd(reinterpret_cast<float4*>(dst + 4), make_float4(cs8[4], cs8[5], cs8[6], cs8[7]));
+        }
+      }
+    }
     __syncwarp();          // the next chunk re-uses the staging buffer
-    return;
-  }
+  } else {
   if constexpr (EPI == EPI_F32) {
     // the previous chunk's TMA reduction must have finished READING this staging buffer
     if (tmC != nullptr) {
@@ -329,7 +362,6 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
   const int c = col + 4 * cl;
   float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
   if (p.bias != nullptr && first_split) b = __ldg(reinterpret_cast<const float4*>(p.bias + c));
-  float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int it = 0; it < 8; ++it) {
     const int rr = it * 4 + rsub;
@@ -341,9 +373,7 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
     if (row >= p.M) continue;
     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
     const size_t off = static_cast<size_t>(row) * p.ldc + c;
-    if constexpr (EPI == EPI_BF16) {
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(a);
-    } else if constexpr (EPI == EPI_F32) {
+    if constexpr (EPI == EPI_F32) {
       float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.C) + off);
       if (p.accumulate || p.k_splits > 1) atomicAdd(dst, a);
       else *dst = a;
@@ -371,26 +401,10 @@ __device__ __forceinline__ void epilogue_chunk_v2(const GemmParams& p, uint8_t* 
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pack_bf16x4(make_float4(d0.x, d0.y, d1.x, d1.y));
       *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C2) + static_cast<size_t>(row) * p.ldc2 + c) =
           pack_bf16x4(make_float4(g0.x, g0.y, g1.x, g1.y));
-    } else if constexpr (EPI == EPI_GELU_BWD) {
-      a = round_bf16x4(a);
-      const float4 dg = unpack_bf16x4(ax.v[it]);      // gelu'(u), stored by the forward epilogue
-      const uint2 pk = pack_bf16x4(make_float4(a.x * dg.x, a.y * dg.y, a.z * dg.z, a.w * dg.w));
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.C) + off) = pk;
-      const float4 orr = unpack_bf16x4(pk);
-      cs.x += orr.x; cs.y += orr.y; cs.z += orr.z; cs.w += orr.w;
-    }
-  }
-  if constexpr (EPI == EPI_GELU_BWD) {
-    if (p.colsum != nullptr) {      // 32 rows of this chunk -> one vector reduction per 4 columns
-#pragma unroll
-      for (int o = 8; o <= 16; o <<= 1) {
-        cs.x += __shfl_xor_sync(0xffffffffu, cs.x, o); cs.y += __shfl_xor_sync(0xffffffffu, cs.y, o);
-        cs.z += __shfl_xor_sync(0xffffffffu, cs.z, o); cs.w += __shfl_xor_sync(0xffffffffu, cs.w, o);
-      }
-      if (rsub == 0) atomicAdd(reinterpret_cast<float4*>(p.colsum + c), cs);
     }
   }
   __syncwarp();
+  }   // fp32-staged epilogues
 }
 
 }  // namespace gxa
