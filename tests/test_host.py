@@ -4,6 +4,7 @@ refuses to run without CUDA (no CPU fallback)."""
 import ctypes as C
 import os
 import re
+import sys
 
 import numpy as np
 import pytest
@@ -142,3 +143,24 @@ def test_dropout_restatement_is_bit_identical_to_the_compiled_mask_function():
         assert np.array_equal(out, ref), (rows, cols, p, site)
     assert L.gxa_dropout_multipliers_host(1.0, 1, 1, 1, 1, np.empty(1, np.float32).ctypes.data) != 0      # p must be < 1
     assert L.gxa_dropout_multipliers_host(0.1, 1, 3, 1, 1, np.empty(1, np.float32).ctypes.data) != 0      # unknown site
+
+
+def test_bench_reference_arm_prints_exactly_one_json_line():
+    """bench.py's contract: ONE JSON line on stdout, whatever native libraries print (descriptor 1 is re-pointed at stderr
+    for the run).  The reference arm runs on the host cores, so this part of the contract is checkable without a GPU; a
+    child process that writes to descriptor 1 behind Python's back stands in for NCCL's banner."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import os, sys, bench; sys.argv = ['bench.py', '--impl', 'reference', '--workload', 'whisper-tiny-c1', "
+            "'--steps', '1', '--warmup', '0', '--ref-batch', '1']; "
+            "bench.claim_stdout(); os.write(1, b'NCCL version 0.0.0 (stand-in)\\n'); "
+            "bench.claim_stdout = lambda: None; bench.main()")
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    out = json.loads(lines[0])
+    assert out["impl"] == "reference" and out["cpu_baseline"]["kind"] in ("reference", "port")
+    assert out["e2e"]["h2d_bytes_per_step"] == 0 and out["value"] > 0
+    assert "NCCL version" in r.stderr
